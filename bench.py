@@ -1,0 +1,414 @@
+#!/usr/bin/env python
+"""bench.py -- statevector hot path on B200 (contract: see the task statement / DESIGN.md).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Primary line (one JSON object on stdout, rank 0):
+  metric  estimator_evals_per_s on BASELINE.json configs[1]: 28-qubit EfficientSU2 reps=4,
+          a batch of 64 parameter sets, 1000-term Heisenberg SparsePauliOp.  One STEP = one
+          batch (64 evals: simulate from |0..0>, then all 1000 terms).  N > 1: every rank runs
+          its own batch on its own GPU (weak scaling, no data-path collective).
+  value   device-resident: gate matrices / Pauli masks prepared on the host before the timed
+          region, timed with CUDA events on the engine's stream.
+  e2e     the same step through the public API (StatevectorEstimator.run(...).result()) from
+          host NumPy inputs, wall clock around a synchronised call.
+  roofline  the gate kernel on an UNFUSABLE 30-qubit stream (Haar SU(4) on random qubit pairs,
+          one pass per gate), CUDA events inside this script; algorithmic bytes = 32 * 2^30
+          per pass.
+  cpu_baseline  the oracle (NumPy evolve + OpenMP C expval) on a bounded sample of the same
+          workload, on this box's host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOAD = "28q EfficientSU2 reps=4 x 64 parameter sets, StatevectorEstimator, 1000-term Heisenberg SparsePauliOp"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=2)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--qubits", type=int, default=28, help="(debug) smaller ansatz; invalidates the metric")
+    ap.add_argument("--batch", type=int, default=64, help="(debug) parameter sets per step")
+    ap.add_argument("--roofline-qubits", type=int, default=30)
+    ap.add_argument("--roofline-gates", type=int, default=24)
+    ap.add_argument("--skip-extras", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------ clocks --
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={gpu_index}", f"--query-gpu={self.FIELDS}",
+                 "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+            out, _ = self.proc.communicate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.splitlines():
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 6:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[2:6]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------- distributed --
+class Dist:
+    """torch.distributed only as plumbing for N > 1 (barrier + max over ranks)."""
+
+    def __init__(self):
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        self.td = None
+        if self.world > 1:
+            import torch.distributed as td
+
+            td.init_process_group(backend="gloo")
+            self.td = td
+
+    def barrier(self):
+        if self.td is not None:
+            self.td.barrier()
+
+    def max(self, v: float) -> float:
+        if self.td is None:
+            return v
+        import torch
+
+        t = torch.tensor([v], dtype=torch.float64)
+        self.td.all_reduce(t, op=self.td.ReduceOp.MAX)
+        return float(t[0])
+
+    def sum(self, v: float) -> float:
+        if self.td is None:
+            return v
+        import torch
+
+        t = torch.tensor([v], dtype=torch.float64)
+        self.td.all_reduce(t, op=self.td.ReduceOp.SUM)
+        return float(t[0])
+
+    def close(self):
+        if self.td is not None:
+            self.td.destroy_process_group()
+
+
+# ---------------------------------------------------------------- our arm ---
+def run_ours(args, dist: Dist) -> dict:
+    from qiskit_b200 import Statevector, StatevectorEstimator, _lib
+    from qiskit_b200 import circuit_library as lib
+    from qiskit_b200.lowering import gate_list_to_stream
+    from qiskit_b200.pauli import pauli_masks
+
+    _lib.require_device()
+    qsv = _lib.load()
+    device = dist.local_rank % max(_lib.device_count(), 1)
+    n, reps, batch = args.qubits, 4, args.batch
+    circuit = lib.efficient_su2_circuit(n, reps)
+    obs = lib.heisenberg_observable(n, 324 if n >= 27 else max(1, (n * (n - 1)) // 4))
+    n_params = 2 * n * (reps + 1)
+    # every rank draws its own parameter batch (weak scaling); rank 0's is BASELINE's seed 0
+    theta = np.random.default_rng(dist.rank).uniform(-np.pi, np.pi, (batch, n_params))
+
+    # ---- device-resident arm: everything the kernels need is prepared up front
+    streams = []
+    for b in range(batch):
+        st = gate_list_to_stream(lib.named_to_matrices(lib.efficient_su2_named(n, reps, theta[b])))
+        streams.append((st, *st.to_c()))
+    z_mask, x_mask, n_y = pauli_masks(obs.paulis.z, obs.paulis.x)
+    phases = np.ascontiguousarray((-1j) ** (n_y % 4), dtype=np.complex128)
+    coeffs = np.asarray(obs.coeffs)
+    out = np.empty(len(z_mask), dtype=np.float64)
+    sv = Statevector.from_int(0, 1 << n, device=device)
+    h = sv._h
+
+    def resident_step():
+        evs = np.empty(batch)
+        for b in range(batch):
+            _lib.check(qsv.qsv_init_basis(h, 0))
+            _lib.check(qsv.qsv_apply_gates(h, streams[b][1], streams[b][2], 0))
+            _lib.check(qsv.qsv_expval_pauli_batch(h, len(z_mask), z_mask.ctypes.data, x_mask.ctypes.data,
+                                                  phases.ctypes.data, out.ctypes.data))
+            evs[b] = float(np.real(np.dot(coeffs, out)))
+        return evs
+
+    for _ in range(args.warmup):
+        evs_res = resident_step()
+    _lib.check(qsv.qsv_reset_counters(h))
+    dist.barrier()
+    _lib.check(qsv.qsv_sync(h))
+    clocks = ClockSampler(device)
+    _lib.check(qsv.qsv_timer_begin(h))
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        evs_res = resident_step()
+    ms = C.c_float()
+    _lib.check(qsv.qsv_timer_end(h, C.byref(ms)))
+    wall_res = time.perf_counter() - t0
+    dist.barrier()
+    clock_info = clocks.stop()
+    ctr = sv.counters()
+    t_res = dist.max(ms.value / 1e3)
+    evals_total = dist.sum(float(batch * args.steps))
+    value = evals_total / t_res
+
+    # ---- end-to-end arm: the public API from host inputs
+    est = StatevectorEstimator(device=device)
+    del sv
+    for _ in range(min(args.warmup, 1)):
+        evs_api = est.run([(circuit, obs, theta)]).result()[0].data.evs
+    dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        evs_api = est.run([(circuit, obs, theta)]).result()[0].data.evs
+    t_e2e = dist.max(time.perf_counter() - t0)
+    e2e_value = evals_total / t_e2e
+    parity_api = float(np.max(np.abs(evs_api - evs_res)))
+    h2d = int(sum(sum(d.nbytes for d in st.data if d is not None) for st, _, _ in streams)
+              + 3 * 8 * len(z_mask) + 16 * len(z_mask))
+    d2h = int(8 * len(z_mask) * batch)
+
+    result = {
+        "metric": "estimator_evals_per_s",
+        "value": value,
+        "unit": "evals/s",
+        "n_gpus": dist.world,
+        "steps": args.steps,
+        "warmup": args.warmup,
+        "ms_per_step": 1e3 * t_res / args.steps,
+        "higher_is_better": True,
+        "scaling": "weak",
+        "vs_baseline": None,
+        "dtype": "f64 (complex128 amplitudes)",
+        "data": "synthetic",
+        "config": {"workload": WORKLOAD if (n == 28 and batch == 64) else f"DEBUG {n}q x {batch}",
+                   "qubits": n, "reps": reps, "batch_per_gpu": batch, "observable_terms": len(z_mask),
+                   "gates_per_eval": 2 * n * (reps + 1) + (n - 1) * reps,
+                   "l2": "state (4.3 GB at 28 q) is larger than L2; no flush needed",
+                   "parallelism": f"replicas x{dist.world} (independent parameter batches)"},
+        "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "api": "StatevectorEstimator.run(pubs).result()",
+                "max_abs_diff_vs_resident": parity_api},
+        "gpu_launches": int(ctr["kernel_launches"]),
+        "passes": {"state_passes_per_eval": ctr["state_passes"] / (batch * args.steps),
+                   "read_passes_per_eval": ctr["read_passes"] / (batch * args.steps)},
+        "clocks": clock_info,
+        "wall_s_resident": wall_res,
+    }
+    if dist.rank == 0 and not args.skip_extras:
+        result["roofline"] = roofline_gate_stream(args, device)
+        result["gate_stream_30q"] = result["roofline"].pop("_detail")
+        if dist.world == 1:
+            result["cpu_baseline"] = cpu_baseline(args, evs_check=None)
+    return result
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        return float(json.load(open(path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy)"
+    return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
+
+
+def roofline_gate_stream(args, device) -> dict:
+    """Unfusable stream: one dense 2-qubit gate per pass at `roofline_qubits` qubits."""
+    from qiskit_b200 import Statevector, _lib
+    from qiskit_b200 import circuit_library as lib
+    from qiskit_b200.lowering import gate_list_to_stream
+
+    qsv = _lib.load()
+    n = args.roofline_qubits
+    free = C.c_uint64()
+    _lib.check(qsv.qsv_device_memory(device, C.byref(free), None))
+    while (16 << n) > 0.8 * free.value and n > 20:
+        n -= 1
+    gates = lib.random_two_qubit_stream(n, args.roofline_gates, seed=7)
+    st = gate_list_to_stream(gates)
+    arr, cnt = st.to_c()
+    sv = Statevector.from_int(0, 1 << n, device=device)
+    h = sv._h
+    for _ in range(3):
+        _lib.check(qsv.qsv_apply_gates(h, arr, min(cnt, 6), _lib.FLAG_NO_FUSION))
+    _lib.check(qsv.qsv_sync(h))
+    _lib.check(qsv.qsv_reset_counters(h))
+    ms = C.c_float()
+    _lib.check(qsv.qsv_timer_begin(h))
+    _lib.check(qsv.qsv_apply_gates(h, arr, cnt, _lib.FLAG_NO_FUSION))
+    _lib.check(qsv.qsv_timer_end(h, C.byref(ms)))
+    ctr = sv.counters()
+    passes = ctr["state_passes"]
+    bytes_per_pass = 32.0 * (1 << n)
+    achieved = passes * bytes_per_pass / (ms.value / 1e3) / 1e9
+    # fused throughput on a QuantumVolume circuit of the same width
+    qv = lib.quantum_volume(n, 4, seed=0)
+    st2 = gate_list_to_stream(qv)
+    arr2, cnt2 = st2.to_c()
+    _lib.check(qsv.qsv_init_basis(h, 0))
+    _lib.check(qsv.qsv_apply_gates(h, arr2, cnt2, 0))
+    _lib.check(qsv.qsv_sync(h))
+    _lib.check(qsv.qsv_reset_counters(h))
+    ms2 = C.c_float()
+    _lib.check(qsv.qsv_timer_begin(h))
+    _lib.check(qsv.qsv_apply_gates(h, arr2, cnt2, 0))
+    _lib.check(qsv.qsv_timer_end(h, C.byref(ms2)))
+    ctr2 = sv.counters()
+    norm = sv._norm2()
+    peak, peak_src = measured_peak()
+    return {
+        "bound": "hbm", "kernel": "k_tile_pass (one dense 2-qubit gate per pass)",
+        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+        "peak_source": peak_src, "traffic": None,
+        "algorithmic_bytes_per_launch": bytes_per_pass,
+        "avg_launch_ms": ms.value / max(passes, 1),
+        "_detail": {
+            "qubits": n, "gates": cnt, "passes": int(passes), "ms": ms.value,
+            "gates_per_s_unfused": cnt / (ms.value / 1e3),
+            "hbm_gbs_unfused": achieved,
+            "qv_depth4_gates": cnt2, "qv_passes": int(ctr2["state_passes"]), "qv_ms": ms2.value,
+            "gates_per_s_fused_qv": cnt2 / (ms2.value / 1e3),
+            "hbm_gbs_fused_qv": ctr2["state_passes"] * bytes_per_pass / (ms2.value / 1e3) / 1e9,
+            "norm_after": norm,
+        },
+    }
+
+
+# ---------------------------------------------------- CPU baseline / oracle --
+def cpu_baseline(args, evs_check=None) -> dict:
+    """The reference's CPU path (NumPy evolve restatement + OpenMP restatement of the Rust
+    expval) on a bounded sample: a few gates and a few terms at full width, scaled to one
+    evaluation = 280 one-qubit + 108 CX gates + 1000 terms."""
+    from oracle import c_expval, gate_matrices as gm, statevector_ref as ref
+
+    try:
+        import psutil
+
+        avail = psutil.virtual_memory().available
+    except Exception:  # noqa: BLE001
+        avail = 32 << 30
+    n = args.qubits
+    while 4 * (16 << n) > 0.7 * avail and n > 16:   # evolve peaks at ~3x state (+ the state)
+        n -= 1
+    cores = os.cpu_count() or 1
+    rng = np.random.default_rng(0)
+    psi = np.zeros(1 << n, dtype=np.complex128)
+    psi[0] = 1.0
+    for q in range(n):  # cheap non-trivial state
+        c_expval.load().oracle_apply_1q(psi.ctypes.data, n, q, np.ascontiguousarray(
+            gm.ry(rng.uniform(0, np.pi)).view(np.float64)).ctypes.data)
+    t_1q = []
+    for q in (0, n // 2, n - 1):
+        t0 = time.perf_counter()
+        psi = ref.evolve_operator(psi, gm.ry(0.3), [q])
+        t_1q.append(time.perf_counter() - t0)
+    t_2q = []
+    for q in (0, n - 2):
+        t0 = time.perf_counter()
+        psi = ref.evolve_operator(psi, gm.cx(), [q, q + 1])
+        t_2q.append(time.perf_counter() - t0)
+    z_only = 1 << (n // 2) | 1
+    t_terms = []
+    t0 = time.perf_counter()
+    c_expval.expval_pauli_no_x(psi, n, z_only)
+    t_terms.append(time.perf_counter() - t0)
+    for x_mask, z_mask in ((0b11, 0), (1 | 1 << (n - 1), 1 | 1 << (n - 1))):
+        t0 = time.perf_counter()
+        c_expval.expval_pauli_with_x(psi, n, z_mask, x_mask, 1.0, x_mask.bit_length() - 1)
+        t_terms.append(time.perf_counter() - t0)
+    scale = 4.0 ** ((args.qubits - n) / 2.0) if n != args.qubits else 1.0   # x2 per qubit
+    reps = 4
+    n_1q = 2 * args.qubits * (reps + 1)
+    n_2q = (args.qubits - 1) * reps
+    t_eval = scale * (n_1q * np.mean(t_1q) + n_2q * np.mean(t_2q) + 1000 * np.mean(t_terms))
+    return {"value": 1.0 / t_eval, "unit": "evals/s", "cores": cores, "kind": "port",
+            "sample": (f"{n}-qubit state: 3 RY + 2 CX through the NumPy restatement of "
+                       f"_evolve_operator, 3 Pauli terms through the OpenMP restatement of "
+                       f"pauli_exp_val.rs; scaled to {n_1q}+{n_2q} gates + 1000 terms"
+                       + (f", x{scale:.0f} for {args.qubits - n} fewer qubits" if scale != 1 else "")),
+            "per_gate_1q_s": float(np.mean(t_1q)), "per_gate_2q_s": float(np.mean(t_2q)),
+            "per_term_s": float(np.mean(t_terms)), "qubits_sampled": n}
+
+
+def run_reference(args, dist: Dist) -> dict | None:
+    if dist.rank != 0:
+        return None
+    vals = []
+    t_all0 = time.perf_counter()
+    for i in range(args.warmup + args.steps):
+        cb = cpu_baseline(args)
+        if i >= args.warmup:
+            vals.append(cb)
+        if time.perf_counter() - t_all0 > 240 and vals:
+            break
+    value = float(np.mean([v["value"] for v in vals]))
+    cb = vals[-1]
+    cb["value"] = value
+    return {
+        "impl": "reference", "metric": "estimator_evals_per_s", "value": value, "unit": "evals/s",
+        "n_gpus": dist.world, "steps": len(vals), "warmup": args.warmup,
+        "ms_per_step": 1e3 * 64 / value, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64 (complex128 amplitudes)", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "note": "reference CPU path (oracle port) on host cores; "
+                   "each step is a bounded sample scaled to one batch"},
+        "cpu_baseline": cb,
+        "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+
+
+def main():
+    args = parse_args()
+    dist = Dist()
+    try:
+        res = run_reference(args, dist) if args.impl == "reference" else run_ours(args, dist)
+        if dist.rank == 0 and res is not None:
+            print(json.dumps(res))
+    finally:
+        dist.close()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,170 @@
+/*
+ * qsv.h -- C ABI of libqsv_b200.so, a B200 (sm_100a) dense statevector engine.
+ *
+ * This is the drop-in boundary for ONE hot path of Qiskit 2.6.0.dev0: dense
+ * statevector simulation behind Statevector.evolve / expectation_value /
+ * probabilities / sample_memory and the StatevectorEstimator / Sampler.  The
+ * reference has no FFI for this path (its C API, crates/cext, exposes no
+ * simulation function), so each entry point below names the
+ * reference function it replaces (paths relative to the reference checkout).
+ * The Python side binds these with ctypes (qiskit_b200/_lib.py); the stub a
+ * Qiskit maintainer would add is in INTEGRATION.md.
+ *
+ * Conventions
+ *   - every function returns an int status: QSV_OK (0) or a QSV_ERR_* code;
+ *     qsv_last_error() returns a thread-local, NUL-terminated message for the
+ *     last failure on the calling thread;
+ *   - no C++ exception, Python object or torch type crosses this boundary:
+ *     plain pointers and sizes only;
+ *   - host pointers are caller-owned and only touched during the call; device
+ *     memory is owned by the opaque qsv_state and released by qsv_destroy;
+ *   - complex128 data is passed as interleaved doubles (re, im);
+ *   - qubit q is bit q of the amplitude index (statevector.py:937); a k-qubit
+ *     matrix is 2^k x 2^k row-major with qargs[0] as the least significant bit
+ *     of its row/column index (crates/circuit/src/gate_matrix.rs:30-50);
+ *   - a handle may be used by one thread at a time, from any thread (every
+ *     entry point selects the handle's device); different handles may be used
+ *     concurrently.
+ */
+#ifndef QSV_H
+#define QSV_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QSV_OK 0
+#define QSV_ERR_INVALID 1     /* bad argument (Python side raises ValueError / QiskitError) */
+#define QSV_ERR_CUDA 2        /* CUDA runtime failure */
+#define QSV_ERR_NOMEM 3       /* device allocation failed */
+#define QSV_ERR_NCCL 4        /* NCCL failure or NCCL not loadable */
+#define QSV_ERR_UNSUPPORTED 5 /* valid request outside what the engine implements */
+#define QSV_ERR_OVERFLOW 6    /* num_qubits too large (pauli_exp_val.rs:44-48 -> OverflowError) */
+
+#define QSV_MAX_GATE_QUBITS 12 /* widest dense matrix qsv_apply_matrix accepts */
+
+/* gate kinds for qsv_apply_gates */
+#define QSV_GATE_MATRIX 0   /* data: 2^k x 2^k row-major complex128 */
+#define QSV_GATE_DIAGONAL 1 /* data: 2^k complex128 diagonal entries */
+#define QSV_GATE_PHASE 2    /* global phase exp(i*params[0]); k = 0 (statevector.py:1026-1028) */
+
+/* flags for qsv_apply_gates */
+#define QSV_FLAG_NO_FUSION 1 /* one pass over the state per gate (roofline measurement mode) */
+
+typedef struct qsv_state qsv_state;
+
+typedef struct qsv_gate {
+    int32_t kind;                        /* QSV_GATE_* */
+    int32_t k;                           /* number of qubits */
+    int32_t qargs[QSV_MAX_GATE_QUBITS];  /* qargs[0] = LSB of the matrix index */
+    const double* data;                  /* host pointer, see kind */
+    double params[4];
+} qsv_gate;
+
+/* cumulative per-handle counters (qsv_get_counters) */
+typedef struct qsv_counters {
+    uint64_t kernel_launches; /* kernels this library launched on the handle's stream */
+    uint64_t state_passes;    /* full read+write sweeps over the amplitude array */
+    uint64_t read_passes;     /* read-only sweeps (expval, probabilities, scan) */
+    uint64_t gates_applied;   /* gates received through the API (before fusion) */
+    uint64_t h2d_bytes;
+    uint64_t d2h_bytes;
+} qsv_counters;
+
+/* ---- library ---------------------------------------------------------- */
+int qsv_version(void);
+const char* qsv_last_error(void);
+int qsv_device_count(int* out);
+/* free / total device memory in bytes */
+int qsv_device_memory(int device, uint64_t* free_bytes, uint64_t* total_bytes);
+
+/* ---- state lifetime: type Statevector (statevector.py:44-113), _data (:88) */
+int qsv_create(qsv_state** out, int n_qubits, int device);
+int qsv_destroy(qsv_state* s);
+/* deep copy on the same device: QuantumState.copy (quantum_state.py:74-76) */
+int qsv_clone(const qsv_state* s, qsv_state** out);
+/* dst <- src (device-to-device); both handles must have the same size and device */
+int qsv_copy_state(qsv_state* dst, const qsv_state* src);
+int qsv_num_qubits(const qsv_state* s, int* out);
+/* Statevector.from_int (statevector.py:790-816): |index> */
+int qsv_init_basis(qsv_state* s, uint64_t index);
+/* host <-> device copies of amplitudes [offset, offset+count) */
+int qsv_upload(qsv_state* s, const double* c128, uint64_t offset, uint64_t count);
+int qsv_download(const qsv_state* s, double* c128, uint64_t offset, uint64_t count);
+int qsv_sync(const qsv_state* s);
+
+/* ---- gate application: Statevector._evolve_operator (statevector.py:925-963) */
+int qsv_apply_matrix(qsv_state* s, const double* mat_rowmajor_c128, int k, const int* qargs);
+int qsv_apply_diagonal(qsv_state* s, const double* diag_c128, int k, const int* qargs);
+/* a whole unrolled instruction stream, i.e. the leaf calls of
+ * Statevector._evolve_instruction (statevector.py:965-1041); enables fusion */
+int qsv_apply_gates(qsv_state* s, const qsv_gate* gates, uint64_t n_gates, int flags);
+/* Statevector._multiply (statevector.py:415-435) and the global-phase update */
+int qsv_scale(qsv_state* s, double re, double im);
+
+/* ---- expectation values: crates/accelerate/src/pauli_exp_val.rs ---------- */
+/* expval_pauli_no_x (:39-65) when x_mask == 0, else expval_pauli_with_x (:70-123).
+ * phase = (-i)^(#Y); x_max is accepted for signature parity and ignored (any set
+ * bit of x_mask splits the pairs). */
+int qsv_expval_pauli(const qsv_state* s, uint64_t z_mask, uint64_t x_mask, double phase_re,
+                     double phase_im, int x_max, double* out);
+/* all terms of a SparsePauliOp (statevector.py:579-583): out[t] = <P_t>, with
+ * phases[t] = (-i)^(#Y_t) as interleaved complex128 */
+int qsv_expval_pauli_batch(const qsv_state* s, uint64_t n_terms, const uint64_t* z_masks,
+                           const uint64_t* x_masks, const double* phases_c128, double* out);
+/* <s|s> and <a|b> = sum conj(a_i) b_i (Statevector.inner, statevector.py:399-413) */
+int qsv_norm2(const qsv_state* s, double* out);
+int qsv_inner(const qsv_state* a, const qsv_state* b, double* out_c128);
+
+/* ---- probabilities and sampling ---------------------------------------- */
+/* Statevector.probabilities (statevector.py:663-668) + _subsystem_probabilities
+ * (quantum_state.py:437-468): host_out[2^m], output bit j = qubit qargs[j];
+ * qargs == NULL means all qubits in order.  Values are clipped to [0, 1]. */
+int qsv_probabilities(const qsv_state* s, const int* qargs, int m, double* host_out);
+/* QuantumState.sample_memory (quantum_state.py:236-265) with the uniforms made
+ * explicit: out_indices[j] = inverse-cdf sample for uniforms[j] (the arithmetic of
+ * numpy.random.Generator.choice(p=...)), under the summation tree documented in
+ * DESIGN.md.  total_out (optional) receives the probability mass sum. */
+int qsv_sample(const qsv_state* s, const int* qargs, int m, const double* uniforms,
+               uint64_t shots, uint64_t* out_indices, double* total_out);
+/* projector used by Statevector.reset (statevector.py:694-719) and
+ * QuantumState.measure (quantum_state.py:314-331): keep the branch where the
+ * qargs bits equal `outcome`, multiply it by `scale`, zero the rest; with
+ * rotate_to_zero the kept branch is moved to the qargs = 0...0 branch. */
+int qsv_collapse(qsv_state* s, const int* qargs, int m, uint64_t outcome, double scale,
+                 int rotate_to_zero);
+/* StatevectorSampler._samples_to_packed_array (statevector_sampler.py:235-251):
+ * indices[shots] -> out[shots * num_bytes]; clbit c takes bit src_bit[c] of the
+ * index (src_bit[c] < 0: constant 0); big-endian bytes, clbit 0 = LSB of the last
+ * byte.  Host-side helper (no device work). */
+int qsv_pack_samples(const uint64_t* indices, uint64_t shots, const int* src_bit, int num_bits,
+                     uint8_t* out);
+
+/* ---- measurement hooks -------------------------------------------------- */
+int qsv_get_counters(const qsv_state* s, qsv_counters* out);
+int qsv_reset_counters(qsv_state* s);
+/* CUDA-event timer on the handle's stream: begin records an event, end records a
+ * second one, synchronises and returns the elapsed milliseconds between them. */
+int qsv_timer_begin(qsv_state* s);
+int qsv_timer_end(qsv_state* s, float* ms_out);
+/* engine tunables, by name ("tile_bits", "low_bits", ...); for experiments */
+int qsv_set_option(qsv_state* s, const char* name, int64_t value);
+/* write a buffer larger than L2 (flush between timed iterations) */
+int qsv_flush_l2(qsv_state* s);
+
+/* ---- sharded states (one process per GPU; NCCL over NVLink) -------------- */
+/* 128-byte ncclUniqueId for the bootstrap; rank 0 creates it and the host side
+ * distributes it (torch.distributed / any channel) */
+int qsv_dist_unique_id(void* out128);
+/* n_qubits total; this rank holds the slab whose top log2(world) index bits are
+ * `rank`; world must be a power of two */
+int qsv_create_dist(qsv_state** out, int n_qubits, int device, int rank, int world,
+                    const void* unique_id128);
+int qsv_dist_info(const qsv_state* s, int* rank, int* world, int* n_local);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QSV_H */

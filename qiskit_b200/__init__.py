@@ -1,0 +1,21 @@
+"""qiskit_b200 -- a B200 (sm_100a) statevector engine behind Qiskit's simulation API.
+
+One hot path of Qiskit, re-built for the GPU: ``Statevector.evolve /
+expectation_value / probabilities / sample_memory``, ``StatevectorEstimator`` and
+``StatevectorSampler`` with ``SparsePauliOp`` observables.  Host code is plain
+Python calling ``libqsv_b200.so`` (hand-written CUDA, C ABI in include/qsv.h)
+through ctypes; there is no PyTorch on the path and no CPU fallback.
+"""
+from .exceptions import QiskitError
+from .circuit import (ClassicalRegister, Gate, Instruction, Parameter, ParameterVector,
+                      QuantumCircuit)
+from .pauli import Pauli, PauliList, SparsePauliOp
+from .statevector import Statevector
+from .primitives import BitArray, StatevectorEstimator, StatevectorSampler
+
+__all__ = [
+    "QiskitError", "QuantumCircuit", "ClassicalRegister", "Parameter", "ParameterVector", "Gate",
+    "Instruction", "Pauli", "PauliList", "SparsePauliOp", "Statevector", "StatevectorEstimator",
+    "StatevectorSampler", "BitArray",
+]
+__version__ = "0.1.0"

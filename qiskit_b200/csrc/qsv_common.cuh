@@ -1,0 +1,101 @@
+// Internal definitions shared by the translation units of libqsv_b200.so.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/qsv.h"
+
+// ---------------------------------------------------------------- errors --
+void qsv_set_error(const char* fmt, ...);
+
+#define QSV_FAIL(code, ...)         \
+    do {                            \
+        qsv_set_error(__VA_ARGS__); \
+        return (code);              \
+    } while (0)
+
+#define QSV_CUDA(expr)                                                                   \
+    do {                                                                                 \
+        cudaError_t err__ = (expr);                                                      \
+        if (err__ != cudaSuccess) {                                                      \
+            qsv_set_error("CUDA error %s at %s:%d: %s", cudaGetErrorName(err__),         \
+                          __FILE__, __LINE__, cudaGetErrorString(err__));                \
+            return err__ == cudaErrorMemoryAllocation ? QSV_ERR_NOMEM : QSV_ERR_CUDA;    \
+        }                                                                                \
+    } while (0)
+
+#define QSV_TRY(expr)                \
+    do {                             \
+        int rc__ = (expr);           \
+        if (rc__ != QSV_OK) return rc__; \
+    } while (0)
+
+// ----------------------------------------------------------------- state --
+struct qsv_dist;  // defined in qsv_dist.cu
+
+struct qsv_state {
+    int n;        // total qubits
+    int n_local;  // qubits held on this device (n - log2(world))
+    int device;
+    cudaStream_t stream;
+    double2* amp;  // 2^n_local amplitudes
+    // reusable device scratch (reduction partials, op tables, cdf levels ...)
+    void* scratch;
+    size_t scratch_bytes;
+    // pinned host staging for small results
+    void* pinned;
+    size_t pinned_bytes;
+    // L2 flush buffer
+    void* flush_buf;
+    size_t flush_bytes;
+    // timer
+    cudaEvent_t ev0, ev1;
+    // tunables
+    int tile_bits;  // T: amplitudes per tile = 2^T
+    int low_bits;   // L: lowest L index bits are always part of a tile (coalescing)
+    int tile_threads;
+    int use_direct;  // use register-resident kernels for single-gate passes
+    int num_sms;
+    qsv_counters ctr;
+    // sharding
+    int rank, world;
+    qsv_dist* dist;
+    // physical position of each logical qubit (identity unless sharded swaps happened)
+    int perm[64];
+};
+
+static inline uint64_t qsv_local_size(const qsv_state* s) { return 1ull << s->n_local; }
+
+int qsv_ensure_scratch(qsv_state* s, size_t bytes);
+int qsv_ensure_pinned(qsv_state* s, size_t bytes);
+
+// --------------------------------------------------------- device helpers --
+__device__ __forceinline__ double2 cmul(double2 a, double2 b) {
+    return make_double2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+__device__ __forceinline__ double2 cfma(double2 a, double2 b, double2 c) {
+    // c + a*b
+    return make_double2(fma(a.x, b.x, fma(-a.y, b.y, c.x)), fma(a.x, b.y, fma(a.y, b.x, c.y)));
+}
+__device__ __forceinline__ double2 cadd(double2 a, double2 b) {
+    return make_double2(a.x + b.x, a.y + b.y);
+}
+
+// insert a zero bit at position p of v
+__host__ __device__ __forceinline__ uint64_t insert_zero(uint64_t v, int p) {
+    uint64_t low = v & ((1ull << p) - 1);
+    return ((v >> p) << (p + 1)) | low;
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}

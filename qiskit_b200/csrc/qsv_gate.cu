@@ -1,0 +1,806 @@
+// Gate application: Statevector._evolve_operator (statevector.py:925-963) and the
+// leaf calls of Statevector._evolve_instruction (:965-1041), re-designed for B200.
+//
+// The reference makes three full out-of-place copies of the state per gate
+// (transpose, zgemm, transpose).  Here a gate stream is partitioned into PASSES:
+// one pass reads and writes every amplitude exactly once (32 bytes of HBM traffic
+// per amplitude) and applies every gate of the pass on a tile of 2^T amplitudes
+// staged in shared memory.  A tile spans T "active" index bits: the lowest L bits
+// (contiguous 16*2^L-byte runs, so global accesses stay coalesced) plus the bits
+// the pass's gates act on.  Everything is in place: no second state buffer.
+#include <algorithm>
+#include <cmath>
+#include <complex>
+
+#include "qsv_common.cuh"
+
+typedef std::complex<double> cplx;
+
+// ------------------------------------------------------------ device ops --
+enum {
+    OP_DENSE1 = 0,   // 2x2 complex
+    OP_DENSE1R = 1,  // 2x2 real
+    OP_DENSE2 = 2,   // 4x4 complex
+    OP_DENSE2R = 3,  // 4x4 real
+    OP_DIAG = 4,     // phase table over <= DIAG_MAX_BITS tile bits
+    OP_MONO = 5,     // generalised permutation on k <= 3 bits: out[r] = coef[r] * in[src[r]]
+};
+
+#define DIAG_MAX_BITS 10
+#define MAX_TILE_BITS 13
+
+struct DevOp {
+    int32_t kind;
+    int32_t k;
+    int32_t bits[DIAG_MAX_BITS];  // tile-local bit positions (matrix bit j -> bits[j])
+    uint32_t data_off;            // offset into the pass data buffer, in double2 units
+    uint32_t aux;                 // MONO: src rows packed 3 bits each; bit 24+r set = row r untouched
+    uint32_t flags;               // MONO: 1 = all coefficients are exactly 1
+    uint32_t pad;
+};
+
+struct PassParams {
+    int T;          // tile bits
+    int nops;
+    int pos[MAX_TILE_BITS];  // ascending global bit position of tile bit b
+    const DevOp* ops;
+    const double2* data;
+};
+
+__device__ __forceinline__ uint32_t insert_zero32(uint32_t v, int p) {
+    uint32_t low = v & ((1u << p) - 1u);
+    return ((v >> p) << (p + 1)) | low;
+}
+
+template <int NT>
+__device__ __forceinline__ void op_dense1(double2* tile, uint32_t tsize, const DevOp* __restrict__ opp,
+                                          const double2* __restrict__ data, bool real) {
+    const int p = opp->bits[0];
+    const uint32_t doff = opp->data_off;
+    const double2 m00 = __ldg(data + doff + 0), m01 = __ldg(data + doff + 1);
+    const double2 m10 = __ldg(data + doff + 2), m11 = __ldg(data + doff + 3);
+    const uint32_t half = tsize >> 1;
+    if (real) {
+#pragma unroll 4
+        for (uint32_t g = threadIdx.x; g < half; g += NT) {
+            uint32_t i0 = insert_zero32(g, p), i1 = i0 | (1u << p);
+            double2 a0 = tile[i0], a1 = tile[i1];
+            tile[i0] = make_double2(fma(m00.x, a0.x, m01.x * a1.x), fma(m00.x, a0.y, m01.x * a1.y));
+            tile[i1] = make_double2(fma(m10.x, a0.x, m11.x * a1.x), fma(m10.x, a0.y, m11.x * a1.y));
+        }
+    } else {
+#pragma unroll 4
+        for (uint32_t g = threadIdx.x; g < half; g += NT) {
+            uint32_t i0 = insert_zero32(g, p), i1 = i0 | (1u << p);
+            double2 a0 = tile[i0], a1 = tile[i1];
+            tile[i0] = cfma(m01, a1, cmul(m00, a0));
+            tile[i1] = cfma(m11, a1, cmul(m10, a0));
+        }
+    }
+}
+
+template <int NT>
+__device__ __forceinline__ void op_dense2(double2* tile, uint32_t tsize, const DevOp* __restrict__ opp,
+                                          const double2* __restrict__ data, bool real) {
+    const int p0 = opp->bits[0], p1 = opp->bits[1];
+    const uint32_t doff = opp->data_off;
+    const int lo = min(p0, p1), hi = max(p0, p1);
+    const uint32_t o1 = 1u << p0, o2 = 1u << p1;
+    const uint32_t quarter = tsize >> 2;
+    if (real) {
+        double m[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) m[i] = __ldg(&data[doff + i].x);
+#pragma unroll 1
+        for (uint32_t g = threadIdx.x; g < quarter; g += NT) {
+            uint32_t b = insert_zero32(insert_zero32(g, lo), hi);
+            double2 a0 = tile[b], a1 = tile[b | o1], a2 = tile[b | o2], a3 = tile[b | o1 | o2];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                double re = m[4 * r] * a0.x, im = m[4 * r] * a0.y;
+                re = fma(m[4 * r + 1], a1.x, re); im = fma(m[4 * r + 1], a1.y, im);
+                re = fma(m[4 * r + 2], a2.x, re); im = fma(m[4 * r + 2], a2.y, im);
+                re = fma(m[4 * r + 3], a3.x, re); im = fma(m[4 * r + 3], a3.y, im);
+                tile[b | ((r & 1) ? o1 : 0u) | ((r & 2) ? o2 : 0u)] = make_double2(re, im);
+            }
+        }
+    } else {
+        double2 m[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) m[i] = __ldg(data + doff + i);
+#pragma unroll 1
+        for (uint32_t g = threadIdx.x; g < quarter; g += NT) {
+            uint32_t b = insert_zero32(insert_zero32(g, lo), hi);
+            double2 a0 = tile[b], a1 = tile[b | o1], a2 = tile[b | o2], a3 = tile[b | o1 | o2];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                double2 acc = cmul(m[4 * r], a0);
+                acc = cfma(m[4 * r + 1], a1, acc);
+                acc = cfma(m[4 * r + 2], a2, acc);
+                acc = cfma(m[4 * r + 3], a3, acc);
+                tile[b | ((r & 1) ? o1 : 0u) | ((r & 2) ? o2 : 0u)] = acc;
+            }
+        }
+    }
+}
+
+template <int NT>
+__device__ __forceinline__ void op_diag(double2* tile, uint32_t tsize, const DevOp* __restrict__ opp,
+                                        const double2* __restrict__ data) {
+    const int d = opp->k;
+    const double2* __restrict__ tab = data + opp->data_off;
+    for (uint32_t j = threadIdx.x; j < tsize; j += NT) {
+        uint32_t idx = 0;
+        for (int b = 0; b < d; ++b) idx |= ((j >> opp->bits[b]) & 1u) << b;
+        tile[j] = cmul(tile[j], __ldg(tab + idx));
+    }
+}
+
+template <int NT>
+__device__ __forceinline__ void op_mono(double2* tile, uint32_t tsize, const DevOp* __restrict__ opp,
+                                        const double2* __restrict__ data) {
+    const int k = opp->k;
+    const uint32_t dim = 1u << k;
+    const uint32_t groups = tsize >> k;
+    const int b0 = opp->bits[0], b1 = opp->bits[1], b2 = opp->bits[2];
+    const uint32_t aux = opp->aux, doff = opp->data_off;
+    // sorted insertion order for the group base
+    int s0 = b0, s1 = k > 1 ? b1 : 31, s2 = k > 2 ? b2 : 31;
+    if (s0 > s1) { int t = s0; s0 = s1; s1 = t; }
+    if (s1 > s2) { int t = s1; s1 = s2; s2 = t; }
+    if (s0 > s1) { int t = s0; s0 = s1; s1 = t; }
+    const bool unit = opp->flags & 1u;
+    for (uint32_t g = threadIdx.x; g < groups; g += NT) {
+        uint32_t b = insert_zero32(g, s0);
+        if (k > 1) b = insert_zero32(b, s1);
+        if (k > 2) b = insert_zero32(b, s2);
+        double2 v[8];
+#pragma unroll
+        for (uint32_t r = 0; r < 8; ++r) {
+            if (r < dim) {
+                uint32_t off = ((r & 1u) << b0) | (k > 1 ? ((r >> 1) & 1u) << b1 : 0u) |
+                               (k > 2 ? ((r >> 2) & 1u) << b2 : 0u);
+                v[r] = tile[b | off];
+            }
+        }
+#pragma unroll
+        for (uint32_t r = 0; r < 8; ++r) {
+            if (r < dim && !((aux >> (24 + r)) & 1u)) {
+                uint32_t src = (aux >> (3 * r)) & 7u;
+                uint32_t off = ((r & 1u) << b0) | (k > 1 ? ((r >> 1) & 1u) << b1 : 0u) |
+                               (k > 2 ? ((r >> 2) & 1u) << b2 : 0u);
+                double2 x = v[0];
+#pragma unroll
+                for (uint32_t c = 1; c < 8; ++c)
+                    if (c == src) x = v[c];
+                tile[b | off] = unit ? x : cmul(__ldg(data + doff + r), x);
+            }
+        }
+    }
+}
+
+// One pass over the state.  Grid = number of tiles; dynamic smem = 16 * 2^T bytes.
+template <int NT>
+__global__ void __launch_bounds__(NT, 512 / NT) k_tile_pass(double2* __restrict__ amp, const PassParams P) {
+    extern __shared__ double2 tile[];
+    __shared__ uint64_t hi_off[1 << (MAX_TILE_BITS - 7)];
+    const int T = P.T;
+    const uint32_t tsize = 1u << T;
+    constexpr int LOGNT = NT == 128 ? 7 : (NT == 256 ? 8 : 9);
+
+    // tile base: blockIdx deposited on the non-active bits
+    uint64_t base = blockIdx.x;
+    for (int b = 0; b < T; ++b) base = insert_zero(base, P.pos[b]);
+    // per-thread offset of tile-local index bits [0, LOGNT) and a table for the rest
+    uint64_t lo_off = 0;
+    for (int b = 0; b < T && b < LOGNT; ++b) lo_off |= (uint64_t)((threadIdx.x >> b) & 1u) << P.pos[b];
+    if (T > LOGNT && threadIdx.x < (1u << (T - LOGNT))) {
+        uint64_t o = 0;
+        for (int b = LOGNT; b < T; ++b) o |= (uint64_t)((threadIdx.x >> (b - LOGNT)) & 1u) << P.pos[b];
+        hi_off[threadIdx.x] = o;
+    }
+    __syncthreads();
+    double2* __restrict__ src = amp + base + lo_off;
+    if (T > LOGNT) {
+        const uint32_t R = 1u << (T - LOGNT);
+#pragma unroll 8
+        for (uint32_t r = 0; r < R; ++r) tile[threadIdx.x + r * NT] = src[hi_off[r]];
+    } else if (threadIdx.x < tsize) {
+        tile[threadIdx.x] = src[0];
+    }
+    __syncthreads();
+
+    for (int i = 0; i < P.nops; ++i) {
+        const DevOp* __restrict__ op = P.ops + i;
+        switch (op->kind) {
+            case OP_DENSE1: op_dense1<NT>(tile, tsize, op, P.data, false); break;
+            case OP_DENSE1R: op_dense1<NT>(tile, tsize, op, P.data, true); break;
+            case OP_DENSE2: op_dense2<NT>(tile, tsize, op, P.data, false); break;
+            case OP_DENSE2R: op_dense2<NT>(tile, tsize, op, P.data, true); break;
+            case OP_DIAG: op_diag<NT>(tile, tsize, op, P.data); break;
+            case OP_MONO: op_mono<NT>(tile, tsize, op, P.data); break;
+        }
+        __syncthreads();
+    }
+
+    if (T > LOGNT) {
+        const uint32_t R = 1u << (T - LOGNT);
+#pragma unroll 8
+        for (uint32_t r = 0; r < R; ++r) src[hi_off[r]] = tile[threadIdx.x + r * NT];
+    } else if (threadIdx.x < tsize) {
+        src[0] = tile[threadIdx.x];
+    }
+}
+
+// Generic dense k-qubit gate, 3 <= k <= 12 (user-supplied unitaries, projectors).
+// One CTA per group of 2^k amplitudes: gather to smem, one warp per output row
+// (coalesced matrix reads, shuffle reduction), scatter back.  In place.
+__global__ void __launch_bounds__(256) k_dense_big(double2* __restrict__ amp, int k,
+                                                   const int* __restrict__ qsorted,
+                                                   const int* __restrict__ qbits,
+                                                   const double2* __restrict__ mat) {
+    extern __shared__ double2 sm[];
+    const uint32_t dim = 1u << k;
+    double2* vec = sm;
+    double2* outv = sm + dim;
+    uint64_t base = blockIdx.x;
+    for (int i = 0; i < k; ++i) base = insert_zero(base, qsorted[i]);
+    for (uint32_t c = threadIdx.x; c < dim; c += blockDim.x) {
+        uint64_t off = 0;
+        for (int i = 0; i < k; ++i) off |= (uint64_t)((c >> i) & 1u) << qbits[i];
+        vec[c] = amp[base | off];
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    for (uint32_t r = warp; r < dim; r += nwarps) {
+        const double2* row = mat + (size_t)r * dim;
+        double re = 0.0, im = 0.0;
+        for (uint32_t c = lane; c < dim; c += 32) {
+            double2 m = __ldg(row + c), v = vec[c];
+            re = fma(m.x, v.x, fma(-m.y, v.y, re));
+            im = fma(m.x, v.y, fma(m.y, v.x, im));
+        }
+        re = warp_sum(re);
+        im = warp_sum(im);
+        if (lane == 0) outv[r] = make_double2(re, im);
+    }
+    __syncthreads();
+    for (uint32_t c = threadIdx.x; c < dim; c += blockDim.x) {
+        uint64_t off = 0;
+        for (int i = 0; i < k; ++i) off |= (uint64_t)((c >> i) & 1u) << qbits[i];
+        amp[base | off] = outv[c];
+    }
+}
+
+// ------------------------------------------------------------- host side --
+struct HGate {
+    int k;
+    int q[QSV_MAX_GATE_QUBITS];  // physical bit of matrix index bit j
+    std::vector<cplx> m;         // 2^k x 2^k row-major (dense / mono) or 2^k (diag)
+    bool diag;
+};
+
+static bool mat_is_diag(const std::vector<cplx>& m, int dim) {
+    for (int r = 0; r < dim; ++r)
+        for (int c = 0; c < dim; ++c)
+            if (r != c && m[(size_t)r * dim + c] != cplx(0.0, 0.0)) return false;
+    return true;
+}
+
+static bool mat_is_real(const std::vector<cplx>& m) {
+    for (const cplx& v : m)
+        if (v.imag() != 0.0) return false;
+    return true;
+}
+
+// exactly one nonzero per row and per column
+static bool mat_is_mono(const std::vector<cplx>& m, int dim, int* src) {
+    std::vector<int> used(dim, 0);
+    for (int r = 0; r < dim; ++r) {
+        int nz = -1;
+        for (int c = 0; c < dim; ++c)
+            if (m[(size_t)r * dim + c] != cplx(0.0, 0.0)) {
+                if (nz >= 0) return false;
+                nz = c;
+            }
+        if (nz < 0 || used[nz]) return false;
+        used[nz] = 1;
+        src[r] = nz;
+    }
+    return true;
+}
+
+static double gate_cost(const HGate& g) {
+    const int dim = 1 << g.k;
+    if (g.diag) return 1.0;
+    int src[1 << 3];
+    if (g.k <= 3 && mat_is_mono(g.m, dim, src)) return 1.0;
+    double c = 4.0 * dim;  // DFMA per amplitude of a dense complex block
+    if (mat_is_real(g.m)) c *= 0.5;
+    return c;
+}
+
+// expand gate g (on its qubits) to the qubit list of `host` (superset), as a dense matrix
+static std::vector<cplx> expand_to(const HGate& g, const int* hq, int hk) {
+    const int hdim = 1 << hk, gdim = 1 << g.k;
+    int where[QSV_MAX_GATE_QUBITS];
+    for (int j = 0; j < g.k; ++j) {
+        where[j] = -1;
+        for (int i = 0; i < hk; ++i)
+            if (hq[i] == g.q[j]) where[j] = i;
+    }
+    std::vector<cplx> out((size_t)hdim * hdim, cplx(0.0, 0.0));
+    for (int r = 0; r < hdim; ++r)
+        for (int c = 0; c < hdim; ++c) {
+            int gr = 0, gc = 0, rest_r = r, rest_c = c;
+            for (int j = 0; j < g.k; ++j) {
+                gr |= ((r >> where[j]) & 1) << j;
+                gc |= ((c >> where[j]) & 1) << j;
+                rest_r &= ~(1 << where[j]);
+                rest_c &= ~(1 << where[j]);
+            }
+            if (rest_r != rest_c) continue;
+            out[(size_t)r * hdim + c] = g.diag ? (gr == gc ? g.m[gr] : cplx(0.0, 0.0)) : g.m[(size_t)gr * gdim + gc];
+        }
+    return out;
+}
+
+static void normalise_diag(HGate& g) {
+    if (g.diag) return;
+    const int dim = 1 << g.k;
+    if (!mat_is_diag(g.m, dim)) return;
+    std::vector<cplx> d(dim);
+    for (int i = 0; i < dim; ++i) d[i] = g.m[(size_t)i * dim + i];
+    g.m.swap(d);
+    g.diag = true;
+}
+
+static bool subset_of(const HGate& a, const HGate& b) {
+    for (int j = 0; j < a.k; ++j) {
+        bool f = false;
+        for (int i = 0; i < b.k; ++i) f |= (b.q[i] == a.q[j]);
+        if (!f) return false;
+    }
+    return true;
+}
+
+// later * earlier on the qubits of `host` (the wider of the two)
+static HGate merge_gates(const HGate& earlier, const HGate& later, const HGate& host) {
+    HGate out;
+    out.k = host.k;
+    memcpy(out.q, host.q, sizeof out.q);
+    const int dim = 1 << host.k;
+    if (earlier.diag && later.diag) {
+        out.diag = true;
+        out.m.assign(dim, cplx(1.0, 0.0));
+        for (int i = 0; i < dim; ++i) {
+            for (const HGate* g : {&earlier, &later}) {
+                int gi = 0;
+                for (int j = 0; j < g->k; ++j)
+                    for (int t = 0; t < host.k; ++t)
+                        if (host.q[t] == g->q[j]) gi |= ((i >> t) & 1) << j;
+                out.m[i] *= g->m[gi];
+            }
+        }
+        return out;
+    }
+    std::vector<cplx> a = expand_to(earlier, host.q, host.k);
+    std::vector<cplx> b = expand_to(later, host.q, host.k);
+    out.diag = false;
+    out.m.assign((size_t)dim * dim, cplx(0.0, 0.0));
+    for (int r = 0; r < dim; ++r)
+        for (int t = 0; t < dim; ++t) {
+            cplx v = b[(size_t)r * dim + t];
+            if (v == cplx(0.0, 0.0)) continue;
+            for (int c = 0; c < dim; ++c) out.m[(size_t)r * dim + c] += v * a[(size_t)t * dim + c];
+        }
+    normalise_diag(out);
+    return out;
+}
+
+// Peephole fusion: fold a gate into the previous gate on its qubits (or the
+// previous gate into it) when one's qubits contain the other's and the merged
+// block is not more expensive than the two apart.
+static void fuse_gates(std::vector<HGate>& gates, int nbits) {
+    std::vector<int> last(nbits, -1);  // index into `out` of the last gate on each bit
+    std::vector<HGate> out;
+    std::vector<char> dead;
+    for (HGate& g : gates) {
+        int cand = -2;
+        bool same = true;
+        for (int j = 0; j < g.k; ++j) {
+            int l = last[g.q[j]];
+            if (cand == -2) cand = l;
+            else if (l != cand) same = false;
+        }
+        bool merged = false;
+        if (g.k > 0 && same && cand >= 0 && !dead[cand] && g.k <= 2 && out[cand].k <= 2) {
+            HGate& h = out[cand];
+            if (subset_of(g, h)) {
+                // h is the most recent gate on all of g's qubits: g folds into h in place
+                HGate mg = merge_gates(h, g, h);
+                if (gate_cost(mg) <= gate_cost(h) + gate_cost(g)) {
+                    h = mg;
+                    merged = true;
+                }
+            }
+        }
+        if (!merged && g.k > 0 && g.k <= 2) {
+            // every earlier gate that sits entirely inside g's qubits and is the last gate on
+            // all of its own qubits can be pulled forward into g
+            for (int j = 0; j < g.k; ++j) {
+                int l = last[g.q[j]];
+                if (l < 0 || dead[l]) continue;
+                HGate& h = out[l];
+                if (h.k > g.k || !subset_of(h, g)) continue;
+                bool is_last = true;
+                for (int t = 0; t < h.k; ++t) is_last &= (last[h.q[t]] == l);
+                if (!is_last) continue;
+                HGate mg = merge_gates(h, g, g);
+                if (gate_cost(mg) <= gate_cost(h) + gate_cost(g)) {
+                    g = mg;
+                    dead[l] = 1;
+                    for (int t = 0; t < h.k; ++t) last[h.q[t]] = -1;
+                }
+            }
+        }
+        if (!merged) {
+            out.push_back(g);
+            dead.push_back(0);
+            for (int j = 0; j < g.k; ++j) last[g.q[j]] = (int)out.size() - 1;
+        }
+    }
+    gates.clear();
+    for (size_t i = 0; i < out.size(); ++i)
+        if (!dead[i]) gates.push_back(std::move(out[i]));
+}
+
+struct PassPlan {
+    std::vector<int> gate_ids;
+    uint64_t qmask;
+};
+
+static int popc64(uint64_t v) { return __builtin_popcountll(v); }
+
+// Greedy partition into passes.  A gate may join the open pass if its qubits are
+// not blocked by an earlier gate that was left for later, and the pass still
+// fits in T bits together with the forced low bits.
+static void plan_passes(const std::vector<HGate>& gates, int n_local, int T, int L, bool no_fusion,
+                        std::vector<PassPlan>& passes) {
+    const size_t G = gates.size();
+    std::vector<char> done(G, 0);
+    size_t first = 0;
+    const uint64_t lowmask = L >= 64 ? ~0ull : ((1ull << L) - 1);
+    const int cap = std::min(T, n_local);
+    while (first < G) {
+        while (first < G && done[first]) ++first;
+        if (first >= G) break;
+        PassPlan p;
+        p.qmask = 0;
+        uint64_t blocked = 0;
+        const uint64_t all = n_local >= 64 ? ~0ull : ((1ull << n_local) - 1);
+        const size_t window = 4096;
+        for (size_t i = first; i < G && i < first + window; ++i) {
+            if (done[i]) continue;
+            uint64_t gm = 0;
+            for (int j = 0; j < gates[i].k; ++j) gm |= 1ull << gates[i].q[j];
+            bool ok = !(gm & blocked);
+            if (ok) {
+                uint64_t u = p.qmask | gm;
+                int need = popc64((u | lowmask) & all);
+                if (need > cap) ok = false;
+                if (no_fusion && !p.gate_ids.empty()) ok = false;
+            }
+            if (ok) {
+                p.qmask |= gm;
+                p.gate_ids.push_back((int)i);
+                done[i] = 1;
+            } else {
+                blocked |= gm;
+                if ((blocked & all) == all) break;
+            }
+            if (no_fusion && !p.gate_ids.empty()) break;
+        }
+        passes.push_back(std::move(p));
+    }
+}
+
+static int launch_tile_pass(qsv_state* s, const PassParams& P, uint64_t ntiles) {
+    const size_t smem = (size_t)16 << P.T;
+    if (ntiles > 0x7fffffffull) QSV_FAIL(QSV_ERR_UNSUPPORTED, "too many tiles for one launch");
+    switch (s->tile_threads) {
+        case 128:
+            QSV_CUDA(cudaFuncSetAttribute(k_tile_pass<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k_tile_pass<128><<<(unsigned)ntiles, 128, smem, s->stream>>>(s->amp, P);
+            break;
+        case 512:
+            QSV_CUDA(cudaFuncSetAttribute(k_tile_pass<512>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k_tile_pass<512><<<(unsigned)ntiles, 512, smem, s->stream>>>(s->amp, P);
+            break;
+        default:
+            QSV_CUDA(cudaFuncSetAttribute(k_tile_pass<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k_tile_pass<256><<<(unsigned)ntiles, 256, smem, s->stream>>>(s->amp, P);
+            break;
+    }
+    QSV_CUDA(cudaGetLastError());
+    s->ctr.kernel_launches++;
+    s->ctr.state_passes++;
+    return QSV_OK;
+}
+
+static int apply_dense_big(qsv_state* s, const HGate& g) {
+    const int k = g.k;
+    const size_t dim = (size_t)1 << k;
+    // scratch layout: [matrix dim*dim double2][qsorted k ints][qbits k ints]
+    size_t mat_bytes = dim * dim * 16;
+    size_t bytes = mat_bytes + 2 * QSV_MAX_GATE_QUBITS * sizeof(int);
+    QSV_TRY(qsv_ensure_scratch(s, bytes));
+    QSV_TRY(qsv_ensure_pinned(s, bytes));
+    QSV_CUDA(cudaStreamSynchronize(s->stream));  // pinned staging reuse
+    char* h = (char*)s->pinned;
+    std::vector<cplx> dense;
+    const cplx* src = g.m.data();
+    if (g.diag) {
+        dense.assign(dim * dim, cplx(0.0, 0.0));
+        for (size_t i = 0; i < dim; ++i) dense[i * dim + i] = g.m[i];
+        src = dense.data();
+    }
+    memcpy(h, src, mat_bytes);
+    int* hs = (int*)(h + mat_bytes);
+    int* hb = hs + QSV_MAX_GATE_QUBITS;
+    for (int i = 0; i < k; ++i) hs[i] = hb[i] = g.q[i];
+    std::sort(hs, hs + k);
+    QSV_CUDA(cudaMemcpyAsync(s->scratch, h, bytes, cudaMemcpyHostToDevice, s->stream));
+    const size_t smem = 2 * dim * 16;
+    QSV_CUDA(cudaFuncSetAttribute(k_dense_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    uint64_t groups = 1ull << (s->n_local - k);
+    if (groups > 0x7fffffffull) QSV_FAIL(QSV_ERR_UNSUPPORTED, "too many groups for one launch");
+    const int* ds = (const int*)((char*)s->scratch + mat_bytes);
+    k_dense_big<<<(unsigned)groups, 256, smem, s->stream>>>(s->amp, k, ds, ds + QSV_MAX_GATE_QUBITS,
+                                                             (const double2*)s->scratch);
+    QSV_CUDA(cudaGetLastError());
+    s->ctr.kernel_launches++;
+    s->ctr.state_passes++;
+    return QSV_OK;
+}
+
+// Build the device ops of one pass into the staging area (no launch).
+static int build_pass(qsv_state* s, const std::vector<HGate>& gates, const PassPlan& plan, int T,
+                      char* stage, size_t stage_cap, size_t& stage_used, char* dev_base,
+                      PassParams& P) {
+    const int n = s->n_local;
+    const int cap = std::min(T, n);
+    uint64_t active = plan.qmask;
+    for (int b = 0; b < n && popc64(active) < cap; ++b) active |= 1ull << b;  // low bits first
+    memset(&P, 0, sizeof P);
+    P.T = popc64(active);
+    int local_of[64];
+    for (int b = 0, t = 0; b < 64; ++b) {
+        local_of[b] = -1;
+        if ((active >> b) & 1ull) {
+            P.pos[t] = b;
+            local_of[b] = t++;
+        }
+    }
+    std::vector<DevOp> ops;
+    std::vector<double2> data;
+    size_t gi = 0;
+    const std::vector<int>& ids = plan.gate_ids;
+    while (gi < ids.size()) {
+        const HGate& g = gates[ids[gi]];
+        DevOp op;
+        memset(&op, 0, sizeof op);
+        if (g.diag) {
+            // runs of consecutive diagonal gates collapse into one phase table
+            uint64_t um = 0;
+            size_t gj = gi;
+            while (gj < ids.size() && gates[ids[gj]].diag) {
+                uint64_t gm = 0;
+                for (int j = 0; j < gates[ids[gj]].k; ++j) gm |= 1ull << gates[ids[gj]].q[j];
+                if (popc64(um | gm) > DIAG_MAX_BITS) break;
+                um |= gm;
+                ++gj;
+            }
+            if (gj == gi)
+                QSV_FAIL(QSV_ERR_UNSUPPORTED, "diagonal gate wider than %d qubits", DIAG_MAX_BITS);
+            int d = 0;
+            int bit_of[64];
+            for (int b = 0; b < 64; ++b)
+                if ((um >> b) & 1ull) {
+                    bit_of[b] = d;
+                    op.bits[d++] = local_of[b];
+                }
+            op.kind = OP_DIAG;
+            op.k = d;
+            op.data_off = (uint32_t)data.size();
+            std::vector<cplx> tab((size_t)1 << d, cplx(1.0, 0.0));
+            for (size_t t = gi; t < gj; ++t) {
+                const HGate& h = gates[ids[t]];
+                for (size_t i = 0; i < tab.size(); ++i) {
+                    int hi = 0;
+                    for (int j = 0; j < h.k; ++j) hi |= (int)((i >> bit_of[h.q[j]]) & 1) << j;
+                    tab[i] *= h.m[hi];
+                }
+            }
+            for (const cplx& v : tab) data.push_back(make_double2(v.real(), v.imag()));
+            ops.push_back(op);
+            gi = gj;
+            continue;
+        }
+        const int dim = 1 << g.k;
+        int srcrow[8];
+        if (g.k <= 3 && mat_is_mono(g.m, dim, srcrow)) {
+            op.kind = OP_MONO;
+            op.k = g.k;
+            for (int j = 0; j < g.k; ++j) op.bits[j] = local_of[g.q[j]];
+            op.data_off = (uint32_t)data.size();
+            bool unit = true;
+            for (int r = 0; r < dim; ++r) {
+                cplx c = g.m[(size_t)r * dim + srcrow[r]];
+                unit &= (c == cplx(1.0, 0.0));
+                op.aux |= (uint32_t)srcrow[r] << (3 * r);
+                if (srcrow[r] == r && c == cplx(1.0, 0.0)) op.aux |= 1u << (24 + r);
+                data.push_back(make_double2(c.real(), c.imag()));
+            }
+            op.flags = unit ? 1u : 0u;
+            ops.push_back(op);
+        } else if (g.k == 1 || g.k == 2) {
+            bool real = mat_is_real(g.m);
+            op.kind = g.k == 1 ? (real ? OP_DENSE1R : OP_DENSE1) : (real ? OP_DENSE2R : OP_DENSE2);
+            op.k = g.k;
+            for (int j = 0; j < g.k; ++j) op.bits[j] = local_of[g.q[j]];
+            op.data_off = (uint32_t)data.size();
+            for (const cplx& v : g.m) data.push_back(make_double2(v.real(), v.imag()));
+            ops.push_back(op);
+        } else {
+            QSV_FAIL(QSV_ERR_UNSUPPORTED, "internal: dense %d-qubit gate reached the tile path", g.k);
+        }
+        ++gi;
+    }
+    size_t ops_bytes = ops.size() * sizeof(DevOp);
+    size_t data_bytes = data.size() * sizeof(double2);
+    size_t off = (stage_used + 15) & ~(size_t)15;
+    if (off + ops_bytes + data_bytes > stage_cap)
+        QSV_FAIL(QSV_ERR_UNSUPPORTED, "internal: op staging overflow");
+    memcpy(stage + off, ops.data(), ops_bytes);
+    memcpy(stage + off + ops_bytes, data.data(), data_bytes);
+    P.nops = (int)ops.size();
+    P.ops = (const DevOp*)(dev_base + off);
+    P.data = (const double2*)(dev_base + off + ops_bytes);
+    stage_used = off + ops_bytes + data_bytes;
+    return QSV_OK;
+}
+
+static bool tile_capable(const HGate& g) {
+    if (g.diag) return g.k <= DIAG_MAX_BITS;
+    if (g.k <= 2) return true;
+    int src[8];
+    return g.k == 3 && mat_is_mono(g.m, 8, src);
+}
+
+// Apply classified gates whose qubits are all local (physical bits < n_local).
+int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
+    const bool no_fusion = flags & QSV_FLAG_NO_FUSION;
+    if (!no_fusion) fuse_gates(gates, s->n_local);
+    size_t start = 0;
+    while (start < gates.size()) {
+        size_t end = start;
+        while (end < gates.size() && tile_capable(gates[end])) ++end;
+        if (end > start) {
+            std::vector<HGate> seg(gates.begin() + start, gates.begin() + end);
+            std::vector<PassPlan> passes;
+            const int T = s->tile_bits;
+            plan_passes(seg, s->n_local, T, s->low_bits, no_fusion, passes);
+            size_t cap = 4096;
+            for (const HGate& g : seg) cap += sizeof(DevOp) + 32 + g.m.size() * 16;
+            cap += passes.size() * (((size_t)16 << DIAG_MAX_BITS) + 64);
+            QSV_TRY(qsv_ensure_scratch(s, cap));
+            QSV_TRY(qsv_ensure_pinned(s, cap));
+            // the pinned staging area and the device op buffer are reused across calls
+            QSV_CUDA(cudaStreamSynchronize(s->stream));
+            std::vector<PassParams> params(passes.size());
+            size_t used = 0;
+            for (size_t i = 0; i < passes.size(); ++i)
+                QSV_TRY(build_pass(s, seg, passes[i], T, (char*)s->pinned, cap, used,
+                                   (char*)s->scratch, params[i]));
+            QSV_CUDA(cudaMemcpyAsync(s->scratch, s->pinned, used, cudaMemcpyHostToDevice, s->stream));
+            for (size_t i = 0; i < passes.size(); ++i)
+                QSV_TRY(launch_tile_pass(s, params[i], 1ull << (s->n_local - params[i].T)));
+        }
+        if (end < gates.size()) {
+            QSV_TRY(apply_dense_big(s, gates[end]));
+            ++end;
+        }
+        start = end;
+    }
+    return QSV_OK;
+}
+
+static int validate_qargs(const qsv_state* s, int k, const int* qargs, const char* who) {
+    if (k < 0 || k > QSV_MAX_GATE_QUBITS)
+        QSV_FAIL(QSV_ERR_INVALID, "%s: k = %d outside [0, %d]", who, k, QSV_MAX_GATE_QUBITS);
+    if (k > s->n) QSV_FAIL(QSV_ERR_INVALID, "%s: %d-qubit gate on a %d-qubit state", who, k, s->n);
+    for (int i = 0; i < k; ++i) {
+        if (qargs[i] < 0 || qargs[i] >= s->n)
+            QSV_FAIL(QSV_ERR_INVALID, "%s: qarg %d out of range for %d qubits", who, qargs[i], s->n);
+        for (int j = 0; j < i; ++j)
+            if (qargs[i] == qargs[j]) QSV_FAIL(QSV_ERR_INVALID, "%s: duplicate qarg %d", who, qargs[i]);
+    }
+    return QSV_OK;
+}
+
+// sharded states: make every qubit the stream needs local (qsv_dist.cu)
+int qsv_dist_apply(qsv_state* s, std::vector<HGate>& gates, int flags);
+
+extern "C" int qsv_apply_gates(qsv_state* s, const qsv_gate* gates, uint64_t n_gates, int flags) {
+    if (!s || (!gates && n_gates)) QSV_FAIL(QSV_ERR_INVALID, "qsv_apply_gates: NULL argument");
+    QSV_CUDA(cudaSetDevice(s->device));
+    std::vector<HGate> hg;
+    hg.reserve(n_gates);
+    cplx gphase(1.0, 0.0);
+    for (uint64_t i = 0; i < n_gates; ++i) {
+        const qsv_gate& g = gates[i];
+        if (g.kind == QSV_GATE_PHASE) {
+            gphase *= std::polar(1.0, g.params[0]);
+            continue;
+        }
+        if (g.kind != QSV_GATE_MATRIX && g.kind != QSV_GATE_DIAGONAL)
+            QSV_FAIL(QSV_ERR_INVALID, "qsv_apply_gates: gate %llu has unknown kind %d",
+                     (unsigned long long)i, g.kind);
+        QSV_TRY(validate_qargs(s, g.k, g.qargs, "qsv_apply_gates"));
+        if (!g.data) QSV_FAIL(QSV_ERR_INVALID, "qsv_apply_gates: gate %llu has no data", (unsigned long long)i);
+        HGate h;
+        h.k = g.k;
+        memset(h.q, 0, sizeof h.q);
+        for (int j = 0; j < g.k; ++j) h.q[j] = g.qargs[j];  // logical; mapped to physical below
+        const size_t dim = (size_t)1 << g.k;
+        const cplx* src = reinterpret_cast<const cplx*>(g.data);
+        if (g.kind == QSV_GATE_DIAGONAL) {
+            h.diag = true;
+            h.m.assign(src, src + dim);
+        } else {
+            h.diag = false;
+            h.m.assign(src, src + dim * dim);
+            normalise_diag(h);
+        }
+        if (h.k == 0) {  // 0-qubit "gate": a scalar
+            gphase *= h.m[0];
+            continue;
+        }
+        hg.push_back(std::move(h));
+    }
+    s->ctr.gates_applied += n_gates;
+    if (gphase != cplx(1.0, 0.0)) {
+        if (hg.empty()) return qsv_scale(s, gphase.real(), gphase.imag());
+        for (cplx& v : hg[0].m) v *= gphase;
+    }
+    if (hg.empty()) return QSV_OK;
+    if (s->world > 1) return qsv_dist_apply(s, hg, flags);
+    return qsv_apply_hgates(s, hg, flags);
+}
+
+extern "C" int qsv_apply_matrix(qsv_state* s, const double* mat, int k, const int* qargs) {
+    if (!s || !mat || (!qargs && k)) QSV_FAIL(QSV_ERR_INVALID, "qsv_apply_matrix: NULL argument");
+    qsv_gate g;
+    memset(&g, 0, sizeof g);
+    g.kind = QSV_GATE_MATRIX;
+    g.k = k;
+    if (k < 0 || k > QSV_MAX_GATE_QUBITS)
+        QSV_FAIL(QSV_ERR_INVALID, "qsv_apply_matrix: k = %d outside [0, %d]", k, QSV_MAX_GATE_QUBITS);
+    for (int i = 0; i < k; ++i) g.qargs[i] = qargs[i];
+    g.data = mat;
+    return qsv_apply_gates(s, &g, 1, 0);
+}
+
+extern "C" int qsv_apply_diagonal(qsv_state* s, const double* diag, int k, const int* qargs) {
+    if (!s || !diag || (!qargs && k)) QSV_FAIL(QSV_ERR_INVALID, "qsv_apply_diagonal: NULL argument");
+    qsv_gate g;
+    memset(&g, 0, sizeof g);
+    g.kind = QSV_GATE_DIAGONAL;
+    g.k = k;
+    if (k < 0 || k > QSV_MAX_GATE_QUBITS)
+        QSV_FAIL(QSV_ERR_INVALID, "qsv_apply_diagonal: k = %d outside [0, %d]", k, QSV_MAX_GATE_QUBITS);
+    for (int i = 0; i < k; ++i) g.qargs[i] = qargs[i];
+    g.data = diag;
+    return qsv_apply_gates(s, &g, 1, 0);
+}
