@@ -109,6 +109,15 @@ def u(theta, phi, lam):  # :318-325
     )
 
 
+def u2(phi, lam):  # :334-346
+    return _c(
+        [
+            [_S2, -cmath.exp(1j * lam) * _S2],
+            [cmath.exp(1j * phi) * _S2, cmath.exp(1j * (phi + lam)) * _S2],
+        ]
+    )
+
+
 def r(theta, phi):  # :283-293
     c_, s_ = math.cos(theta / 2), math.sin(theta / 2)
     return _c(
@@ -195,7 +204,7 @@ def cswap():  # control bit 0, swaps bits 1 and 2
 
 BY_NAME = {
     "id": identity, "h": h, "x": x, "y": y, "z": z, "s": s, "sdg": sdg, "t": t, "tdg": tdg,
-    "sx": sx, "sxdg": sxdg, "rx": rx, "ry": ry, "rz": rz, "p": p, "u": u, "u3": u, "r": r,
+    "sx": sx, "sxdg": sxdg, "rx": rx, "ry": ry, "rz": rz, "p": p, "u": u, "u3": u, "u2": u2, "r": r,
     "u1": p, "cx": cx, "cy": cy, "cz": cz, "ch": ch, "cp": cp, "cu1": cp, "crx": crx,
     "cry": cry, "crz": crz, "swap": swap, "iswap": iswap, "rxx": rxx, "ryy": ryy,
     "rzz": rzz, "rzx": rzx, "ccx": ccx, "ccz": ccz, "cswap": cswap,

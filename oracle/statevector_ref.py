@@ -344,7 +344,7 @@ def _obj_array(nested):
     subs = [_obj_array(v) for v in nested]
     out = np.empty((len(subs),) + subs[0].shape, dtype=object)
     for i, sub in enumerate(subs):
-        out[i] = sub
+        out[i] = sub[()] if sub.ndim == 0 else sub
     return out
 
 

@@ -6,6 +6,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <complex>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -69,9 +70,26 @@ struct qsv_state {
     qsv_dist* dist;
     // physical position of each logical qubit (identity unless sharded swaps happened)
     int perm[64];
+    // scratch copy of the state used by basis-change expectation values (lazily allocated,
+    // shares this handle's stream; owned by this handle)
+    qsv_state* aux;
+    int owns_stream;
 };
 
+int qsv_state_alloc(qsv_state** out, int n_qubits, int n_local, int device, cudaStream_t share_stream);
+
 static inline uint64_t qsv_local_size(const qsv_state* s) { return 1ull << s->n_local; }
+
+// a gate after parsing: matrix on physical bit positions
+typedef std::complex<double> cplx;
+struct HGate {
+    int k;
+    int q[QSV_MAX_GATE_QUBITS];  // physical bit of matrix index bit j
+    std::vector<cplx> m;         // 2^k x 2^k row-major (dense / mono) or 2^k (diag)
+    bool diag;
+};
+// apply gates whose qubits are all local physical bits (qsv_gate.cu)
+int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags);
 
 int qsv_ensure_scratch(qsv_state* s, size_t bytes);
 int qsv_ensure_pinned(qsv_state* s, size_t bytes);

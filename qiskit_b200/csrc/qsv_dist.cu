@@ -4,7 +4,6 @@
 
 #include <complex>
 
-struct HGate;
 
 void qsv_dist_free(qsv_state* s) { (void)s; }
 

@@ -95,6 +95,94 @@ __global__ void __launch_bounds__(EV_THREADS) k_expval_batch(const double2* __re
     }
 }
 
+// All Z-type terms of an observable in ONE streaming pass.
+//   <Z^m> = sum_i (-1)^popc(i & m) p_i  is the Walsh-Hadamard transform of p at m.
+// A warp takes 256 consecutive amplitudes (lane l holds elements r*32 + l, r = 0..7: coalesced
+// 512-byte loads), transforms them in place (3 register stages + 5 shuffle stages), parks the
+// 256 coefficients in shared memory, and then every lane serves its own terms
+// t = jj*32 + lane: coefficient index = low 8 bits of z_t, sign = parity of the remaining mask
+// bits against the chunk index.  Cost per amplitude ~30 instructions, independent of the
+// number of terms (up to WHT_JJ*32 per launch).
+#define WHT_JJ 16
+#define WHT_TERMS (WHT_JJ * 32)
+#define WHT_WARPS 8
+
+__global__ void __launch_bounds__(32 * WHT_WARPS) k_expval_z_wht(const double2* __restrict__ amp,
+                                                                 uint64_t nchunks, uint64_t chunk_base,
+                                                                 const uint64_t* __restrict__ zmasks,
+                                                                 int nterms, double* __restrict__ partials,
+                                                                 int partial_stride) {
+    __shared__ double wsm[WHT_WARPS][256];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint64_t zt[WHT_JJ];
+    double acc[WHT_JJ];
+#pragma unroll
+    for (int jj = 0; jj < WHT_JJ; ++jj) {
+        const int t = jj * 32 + lane;
+        zt[jj] = t < nterms ? zmasks[t] : 0ull;
+        acc[jj] = 0.0;
+    }
+    for (uint64_t chunk = blockIdx.x * (uint64_t)WHT_WARPS + warp; chunk < nchunks;
+         chunk += (uint64_t)gridDim.x * WHT_WARPS) {
+        const double2* src = amp + chunk * 256 + lane;
+        double p[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            const double2 a = src[r * 32];
+            p[r] = a.x * a.x + a.y * a.y;
+        }
+#pragma unroll
+        for (int sft = 1; sft < 8; sft <<= 1) {
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                if (!(r & sft)) {
+                    const double a = p[r], b = p[r | sft];
+                    p[r] = a + b;
+                    p[r | sft] = a - b;
+                }
+            }
+        }
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                const double other = __shfl_xor_sync(0xffffffffu, p[r], o);
+                p[r] = (lane & o) ? other - p[r] : p[r] + other;
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 8; ++r) wsm[warp][r * 32 + lane] = p[r];
+        __syncwarp();
+        const uint64_t gchunk = chunk | chunk_base;
+#pragma unroll
+        for (int jj = 0; jj < WHT_JJ; ++jj) {
+            if (jj * 32 < nterms) {
+                double v = wsm[warp][zt[jj] & 255ull];
+                if (__popcll((zt[jj] >> 8) & gchunk) & 1) v = -v;
+                acc[jj] += v;
+            }
+        }
+        __syncwarp();
+    }
+    // reduce the WHT_WARPS warps of the block, term by term
+    __syncthreads();
+#pragma unroll
+    for (int jj = 0; jj < WHT_JJ; ++jj) {
+        if (jj * 32 < nterms) {
+            wsm[warp][lane] = acc[jj];
+            __syncthreads();
+            if (warp == 0) {
+                double v = 0.0;
+#pragma unroll
+                for (int w = 0; w < WHT_WARPS; ++w) v += wsm[w][lane];
+                const int t = jj * 32 + lane;
+                if (t < nterms) partials[(size_t)t * partial_stride + blockIdx.x] = v;
+            }
+            __syncthreads();
+        }
+    }
+}
+
 // out[t] = sum_b partials[t][b], one block per term, fixed order
 __global__ void __launch_bounds__(EV_THREADS) k_reduce_partials(const double* __restrict__ partials,
                                                                 int nblocks, int partial_stride,
@@ -157,6 +245,89 @@ static int phase_selector(double re, double im, int* sel) {
     return QSV_OK;
 }
 
+struct TermItem {
+    uint64_t x, z;  // physical masks
+    int sel;        // phase selector: phase = (-i)^sel
+    int ny;         // number of Y factors: popc(x & z)
+    uint64_t idx;   // position in the caller's arrays
+};
+
+// Z-type terms of `st` (masks in zlist) -> d_res[slot0 ...]; one WHT pass per WHT_TERMS terms.
+static int run_wht_terms(qsv_state* st, const std::vector<uint64_t>& zlist, double* d_res,
+                         qsv_counters* ctr) {
+    const uint64_t count = qsv_local_size(st);
+    const uint64_t nchunks = count >> 8;
+    const uint64_t chunk_base = st->world > 1 ? ((uint64_t)st->rank << (st->n_local - 8)) : 0;
+    uint64_t blocks64 = (nchunks + WHT_WARPS - 1) / WHT_WARPS;
+    uint64_t cap = (uint64_t)st->num_sms * 4;
+    if (blocks64 > cap) blocks64 = cap;
+    const int blocks = (int)blocks64;
+    // scratch (of st): [partials WHT_TERMS x blocks][z masks WHT_TERMS]
+    const size_t part_bytes = (size_t)WHT_TERMS * blocks * sizeof(double);
+    const size_t z_off = (part_bytes + 255) & ~(size_t)255;
+    QSV_TRY(qsv_ensure_scratch(st, z_off + WHT_TERMS * sizeof(uint64_t) + 256));
+    double* d_part = (double*)st->scratch;
+    uint64_t* d_z = (uint64_t*)((char*)st->scratch + z_off);
+    for (size_t p0 = 0; p0 < zlist.size(); p0 += WHT_TERMS) {
+        const int nt = (int)std::min<size_t>(WHT_TERMS, zlist.size() - p0);
+        // pageable source: the copy is staged by the runtime before the call returns
+        QSV_CUDA(cudaMemcpyAsync(d_z, zlist.data() + p0, nt * sizeof(uint64_t), cudaMemcpyHostToDevice,
+                                 st->stream));
+        k_expval_z_wht<<<blocks, 32 * WHT_WARPS, 0, st->stream>>>(st->amp, nchunks, chunk_base, d_z, nt,
+                                                                  d_part, blocks);
+        k_reduce_partials<<<nt, EV_THREADS, 0, st->stream>>>(d_part, blocks, blocks, d_res + p0);
+        QSV_CUDA(cudaGetLastError());
+        ctr->kernel_launches += 2;
+        ctr->read_passes += 1;
+        ctr->h2d_bytes += nt * sizeof(uint64_t);
+    }
+    return QSV_OK;
+}
+
+// x-type terms evaluated directly: one pass per (x_mask, <= EV_TERMS terms)
+static int run_direct_terms(qsv_state* s, const std::vector<TermItem>& items,
+                            const std::vector<size_t>& which, double* d_res_base,
+                            std::vector<uint64_t>& result_slot, uint64_t& slot) {
+    std::vector<size_t> order(which);
+    std::stable_sort(order.begin(), order.end(),
+                     [&](size_t a, size_t b) { return items[a].x < items[b].x; });
+    const uint64_t count = qsv_local_size(s);
+    const uint64_t local_mask = count - 1;
+    const uint64_t index_base = s->world > 1 ? ((uint64_t)s->rank << s->n_local) : 0;
+    const int blocks = grid_for(s, count);
+    double* d_part = (double*)s->scratch;
+    for (size_t p = 0; p < order.size();) {
+        TermBatch B;
+        memset(&B, 0, sizeof B);
+        B.x_mask = items[order[p]].x;
+        B.split = B.x_mask ? __builtin_ctzll(B.x_mask) : -1;
+        if (B.x_mask & ~local_mask)
+            QSV_FAIL(QSV_ERR_UNSUPPORTED, "expval: X/Y factor on a sharded (global) qubit");
+        size_t first = p;
+        while (p < order.size() && items[order[p]].x == B.x_mask && B.nterms < EV_TERMS) {
+            B.z_mask[B.nterms] = items[order[p]].z;
+            B.phase_sel[B.nterms] = items[order[p]].sel;
+            ++B.nterms;
+            ++p;
+        }
+        k_expval_batch<<<blocks, EV_THREADS, 0, s->stream>>>(s->amp, count, index_base, B, d_part, blocks);
+        k_reduce_partials<<<B.nterms, EV_THREADS, 0, s->stream>>>(d_part, blocks, blocks, d_res_base + slot);
+        QSV_CUDA(cudaGetLastError());
+        s->ctr.kernel_launches += 2;
+        s->ctr.read_passes += 1;
+        for (int t = 0; t < B.nterms; ++t) result_slot[items[order[first + t]].idx] = slot + t;
+        slot += B.nterms;
+    }
+    return QSV_OK;
+}
+
+// Qubit-wise-commuting family: every member is, on each qubit, either I or the family's basis
+struct QwcGroup {
+    uint64_t xb, zb;  // basis per qubit: (x,z) = (1,0) X, (1,1) Y, (0,1) Z, (0,0) unset
+    std::vector<size_t> members;
+    int distinct_x;
+};
+
 extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, const uint64_t* z_masks,
                                       const uint64_t* x_masks, const double* phases, double* out) {
     qsv_state* s = const_cast<qsv_state*>(cs);
@@ -165,74 +336,175 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
     if (n_terms == 0) return QSV_OK;
     QSV_CUDA(cudaSetDevice(s->device));
     const uint64_t full = s->n >= 64 ? ~0ull : ((1ull << s->n) - 1);
-    // group terms by x_mask (physical bits), preserving order inside a group
-    struct Item { uint64_t x, z; int sel; uint64_t idx; };
-    std::vector<Item> items(n_terms);
+    std::vector<TermItem> items(n_terms);
     for (uint64_t t = 0; t < n_terms; ++t) {
         if ((z_masks[t] | x_masks[t]) & ~full)
             QSV_FAIL(QSV_ERR_INVALID, "qsv_expval_pauli_batch: term %llu has mask bits beyond qubit %d",
                      (unsigned long long)t, s->n - 1);
         int sel = 0;
         if (phases) QSV_TRY(phase_selector(phases[2 * t], phases[2 * t + 1], &sel));
-        items[t] = Item{map_mask(s, x_masks[t]), map_mask(s, z_masks[t]), sel, t};
-    }
-    std::vector<uint64_t> order(n_terms);
-    for (uint64_t t = 0; t < n_terms; ++t) order[t] = t;
-    std::stable_sort(order.begin(), order.end(),
-                     [&](uint64_t a, uint64_t b) { return items[a].x < items[b].x; });
-    // batches
-    std::vector<TermBatch> batches;
-    std::vector<std::vector<uint64_t>> batch_terms;
-    for (uint64_t p = 0; p < n_terms;) {
-        TermBatch B;
-        memset(&B, 0, sizeof B);
-        B.x_mask = items[order[p]].x;
-        B.split = B.x_mask ? __builtin_ctzll(B.x_mask) : -1;
-        std::vector<uint64_t> ids;
-        while (p < n_terms && items[order[p]].x == B.x_mask && B.nterms < EV_TERMS) {
-            B.z_mask[B.nterms] = items[order[p]].z;
-            B.phase_sel[B.nterms] = items[order[p]].sel;
-            ids.push_back(items[order[p]].idx);
-            ++B.nterms;
-            ++p;
-        }
-        batches.push_back(B);
-        batch_terms.push_back(ids);
+        TermItem it;
+        it.x = map_mask(s, x_masks[t]);
+        it.z = map_mask(s, z_masks[t]);
+        it.sel = sel;
+        it.ny = __builtin_popcountll(it.x & it.z);
+        it.idx = t;
+        items[t] = it;
     }
     const uint64_t count = qsv_local_size(s);
-    const uint64_t local_mask = count - 1;
-    const uint64_t index_base = s->world > 1 ? ((uint64_t)s->rank << s->n_local) : 0;
     const int blocks = grid_for(s, count);
-    // scratch: partials [EV_TERMS][blocks] per batch is reused; results [n_terms]
+    // device results: one double per term, slots assigned as work is issued
     const size_t part_bytes = (size_t)EV_TERMS * blocks * sizeof(double);
-    const size_t res_off = (part_bytes + 255) & ~(size_t)255;
+    const size_t wht_bytes = (size_t)WHT_TERMS * (s->num_sms * 4) * sizeof(double) + WHT_TERMS * 8 + 512;
+    const size_t res_off = ((part_bytes > wht_bytes ? part_bytes : wht_bytes) + 255) & ~(size_t)255;
     QSV_TRY(qsv_ensure_scratch(s, res_off + n_terms * sizeof(double) + 256));
-    double* d_part = (double*)s->scratch;
     double* d_res = (double*)((char*)s->scratch + res_off);
     std::vector<uint64_t> result_slot(n_terms);
+    std::vector<double> factor(n_terms, 1.0);  // multiplies the device value on the host
     uint64_t slot = 0;
-    for (size_t b = 0; b < batches.size(); ++b) {
-        TermBatch& B = batches[b];
-        if (B.x_mask & ~local_mask) {
-            // a pair partner lives on another rank: bring the X qubits local first
-            QSV_TRY(qsv_dist_localize_xmask(s, B.x_mask));
-            QSV_FAIL(QSV_ERR_UNSUPPORTED, "internal: x_mask with global bits after localisation");
+    const bool wht_ok = s->n_local >= 8;
+
+    // --- 1. Z-type terms: one WHT pass
+    std::vector<size_t> zterms, xterms;
+    for (size_t t = 0; t < n_terms; ++t) (items[t].x == 0 && wht_ok ? zterms : xterms).push_back(t);
+    if (!zterms.empty()) {
+        std::vector<uint64_t> zl(zterms.size());
+        for (size_t i = 0; i < zterms.size(); ++i) {
+            zl[i] = items[zterms[i]].z;
+            result_slot[items[zterms[i]].idx] = slot + i;
         }
-        k_expval_batch<<<blocks, EV_THREADS, 0, s->stream>>>(s->amp, count, index_base, B, d_part, blocks);
-        k_reduce_partials<<<B.nterms, EV_THREADS, 0, s->stream>>>(d_part, blocks, blocks, d_res + slot);
-        QSV_CUDA(cudaGetLastError());
-        s->ctr.kernel_launches += 2;
-        s->ctr.read_passes += 1;
-        for (int t = 0; t < B.nterms; ++t) result_slot[batch_terms[b][t]] = slot + t;
-        slot += B.nterms;
+        QSV_TRY(run_wht_terms(s, zl, d_res + slot, &s->ctr));
+        slot += zterms.size();
     }
+
+    // --- 2. X-type terms: qubit-wise-commuting families
+    std::vector<QwcGroup> groups;
+    std::vector<size_t> direct;
+    if (wht_ok && s->world == 1) {
+        for (size_t t : xterms) {
+            const TermItem& it = items[t];
+            const uint64_t supp = it.x | it.z;
+            bool placed = false;
+            for (QwcGroup& g : groups) {
+                const uint64_t set = (g.xb | g.zb) & supp;  // qubits where both have an opinion
+                if (((g.xb ^ it.x) & set) || ((g.zb ^ it.z) & set)) continue;
+                g.xb |= it.x;
+                g.zb |= it.z;
+                g.members.push_back(t);
+                placed = true;
+                break;
+            }
+            if (!placed) {
+                QwcGroup g;
+                g.xb = it.x;
+                g.zb = it.z;
+                g.members.push_back(t);
+                groups.push_back(g);
+            }
+        }
+    } else {
+        direct = xterms;
+    }
+    // decide per family: rotate a scratch copy into the Z basis (cost ~ 1 copy + gate passes +
+    // 1 read pass) or evaluate every distinct x_mask directly (one read pass each)
+    std::vector<QwcGroup*> rotated;
+    for (QwcGroup& g : groups) {
+        std::vector<uint64_t> xs;
+        for (size_t t : g.members) xs.push_back(items[t].x);
+        std::sort(xs.begin(), xs.end());
+        g.distinct_x = (int)(std::unique(xs.begin(), xs.end()) - xs.begin());
+        const int nrot = __builtin_popcountll(g.xb);
+        const double cost_rot = 2.0 + 2.0 * ((nrot + 7) / 8) + 1.0;  // in read-pass units
+        if ((double)g.distinct_x > cost_rot) rotated.push_back(&g);
+        else direct.insert(direct.end(), g.members.begin(), g.members.end());
+    }
+    if (!rotated.empty() && !s->aux) {
+        qsv_state* aux = nullptr;
+        int rc = qsv_state_alloc(&aux, s->n, s->n_local, s->device, s->stream);
+        if (rc == QSV_OK) {
+            aux->tile_bits = s->tile_bits;
+            aux->low_bits = s->low_bits;
+            aux->tile_threads = s->tile_threads;
+            aux->use_direct = s->use_direct;
+            s->aux = aux;
+        } else if (rc == QSV_ERR_NOMEM) {
+            for (QwcGroup* g : rotated) direct.insert(direct.end(), g->members.begin(), g->members.end());
+            rotated.clear();  // no room for a scratch copy: fall back to direct passes
+        } else {
+            return rc;
+        }
+    }
+    if (!rotated.empty()) {
+        qsv_state* aux = s->aux;
+        // current per-qubit basis of the scratch copy (starts as the state itself: all Z)
+        uint64_t cur_x = 0, cur_z = 0;
+        bool have_copy = false;
+        const double r2 = 0.70710678118654752440;
+        for (QwcGroup* g : rotated) {
+            if (!have_copy) {
+                QSV_CUDA(cudaMemcpyAsync(aux->amp, s->amp, (size_t)16 << s->n_local,
+                                         cudaMemcpyDeviceToDevice, s->stream));
+                s->ctr.state_passes++;
+                have_copy = true;
+                cur_x = cur_z = 0;
+            }
+            // per rotated qubit: V_new * V_cur^dagger with V_X = H, V_Y = H S^dagger, V_Z = I
+            std::vector<HGate> layer;
+            for (int q = 0; q < s->n_local; ++q) {
+                const uint64_t b = 1ull << q;
+                const int want = (g->xb & b) ? ((g->zb & b) ? 2 : 1) : 0;           // 0 Z/unset, 1 X, 2 Y
+                const int have = (cur_x & b) ? ((cur_z & b) ? 2 : 1) : 0;
+                if (want == have) continue;
+                const cplx I(0.0, 1.0);
+                cplx vx[4] = {r2, r2, r2, -r2};                       // H
+                cplx vy[4] = {r2, -I * r2, r2, I * r2};               // H S^dagger
+                cplx id[4] = {1.0, 0.0, 0.0, 1.0};
+                const cplx* vn = want == 1 ? vx : (want == 2 ? vy : id);
+                const cplx* vc = have == 1 ? vx : (have == 2 ? vy : id);
+                HGate hg;
+                hg.k = 1;
+                memset(hg.q, 0, sizeof hg.q);
+                hg.q[0] = q;
+                hg.diag = false;
+                hg.m.resize(4);
+                for (int r = 0; r < 2; ++r)
+                    for (int c = 0; c < 2; ++c)  // (vn * vc^dagger)[r][c] = sum_k vn[r][k] conj(vc[c][k])
+                        hg.m[r * 2 + c] = vn[r * 2 + 0] * std::conj(vc[c * 2 + 0]) +
+                                          vn[r * 2 + 1] * std::conj(vc[c * 2 + 1]);
+                layer.push_back(hg);
+                cur_x = (cur_x & ~b) | ((want ? b : 0));
+                cur_z = (cur_z & ~b) | ((want == 2 ? b : 0));
+            }
+            if (!layer.empty()) {
+                const uint64_t before_l = aux->ctr.kernel_launches, before_p = aux->ctr.state_passes;
+                QSV_TRY(qsv_apply_hgates(aux, layer, 0));
+                s->ctr.kernel_launches += aux->ctr.kernel_launches - before_l;
+                s->ctr.state_passes += aux->ctr.state_passes - before_p;
+            }
+            // in the rotated frame every member is a Z string on its support
+            std::vector<uint64_t> zl(g->members.size());
+            for (size_t i = 0; i < g->members.size(); ++i) {
+                const TermItem& it = items[g->members[i]];
+                zl[i] = it.x | it.z;
+                result_slot[it.idx] = slot + i;
+                // Re((-i)^(sel - ny)) corrects a caller-supplied phase that differs from (-i)^ny
+                const int d = ((it.sel - it.ny) % 4 + 4) % 4;
+                factor[it.idx] = d == 0 ? 1.0 : (d == 2 ? -1.0 : 0.0);
+            }
+            QSV_TRY(run_wht_terms(aux, zl, d_res + slot, &s->ctr));
+            // run_wht_terms wrote through aux's scratch into this handle's d_res: same stream
+            slot += g->members.size();
+        }
+    }
+    if (!direct.empty()) QSV_TRY(run_direct_terms(s, items, direct, d_res, result_slot, slot));
+
     if (s->world > 1) QSV_TRY(qsv_dist_allreduce_sum(s, d_res, n_terms));
     QSV_TRY(qsv_ensure_pinned(s, n_terms * sizeof(double)));
     QSV_CUDA(cudaMemcpyAsync(s->pinned, d_res, n_terms * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
     QSV_CUDA(cudaStreamSynchronize(s->stream));
     s->ctr.d2h_bytes += n_terms * sizeof(double);
     const double* h = (const double*)s->pinned;
-    for (uint64_t t = 0; t < n_terms; ++t) out[t] = h[result_slot[t]];
+    for (uint64_t t = 0; t < n_terms; ++t) out[t] = factor[t] * h[result_slot[t]];
     return QSV_OK;
 }
 

@@ -14,8 +14,6 @@
 
 #include "qsv_common.cuh"
 
-typedef std::complex<double> cplx;
-
 // ------------------------------------------------------------ device ops --
 enum {
     OP_DENSE1 = 0,   // 2x2 complex
@@ -232,6 +230,69 @@ __global__ void __launch_bounds__(NT, 512 / NT) k_tile_pass(double2* __restrict_
     }
 }
 
+// ---- register-resident kernels for a pass that holds a single dense 1- or 2-qubit gate ----
+// No shared-memory staging: each thread loads its 2 or 4 amplitudes, multiplies by the matrix
+// (kernel parameter, so the entries are constant-bank operands of the DFMAs) and stores.
+// Consecutive threads take consecutive groups, so for targets >= bit 5 every warp access is
+// one contiguous 512-byte run; for low targets the paired loads of a thread share sectors.
+struct Mat2 { double2 m[4]; };
+struct Mat4 { double2 m[16]; };
+
+template <bool REAL>
+__global__ void __launch_bounds__(256) k_direct1(double2* __restrict__ amp, uint64_t half, int p,
+                                                 const __grid_constant__ Mat2 M) {
+    const uint64_t bit = 1ull << p;
+    const uint64_t stride = (uint64_t)gridDim.x * 256;
+#pragma unroll 2
+    for (uint64_t g = blockIdx.x * 256ull + threadIdx.x; g < half; g += stride) {
+        const uint64_t i0 = insert_zero(g, p), i1 = i0 | bit;
+        const double2 a0 = amp[i0], a1 = amp[i1];
+        double2 r0, r1;
+        if (REAL) {
+            r0 = make_double2(fma(M.m[0].x, a0.x, M.m[1].x * a1.x), fma(M.m[0].x, a0.y, M.m[1].x * a1.y));
+            r1 = make_double2(fma(M.m[2].x, a0.x, M.m[3].x * a1.x), fma(M.m[2].x, a0.y, M.m[3].x * a1.y));
+        } else {
+            r0 = cfma(M.m[1], a1, cmul(M.m[0], a0));
+            r1 = cfma(M.m[3], a1, cmul(M.m[2], a0));
+        }
+        amp[i0] = r0;
+        amp[i1] = r1;
+    }
+}
+
+template <bool REAL>
+__global__ void __launch_bounds__(256) k_direct2(double2* __restrict__ amp, uint64_t quarter, int lo,
+                                                 int hi, uint64_t o1, uint64_t o2,
+                                                 const __grid_constant__ Mat4 M) {
+    const uint64_t stride = (uint64_t)gridDim.x * 256;
+#pragma unroll 2
+    for (uint64_t g = blockIdx.x * 256ull + threadIdx.x; g < quarter; g += stride) {
+        const uint64_t b = insert_zero(insert_zero(g, lo), hi);
+        const double2 a0 = amp[b], a1 = amp[b | o1], a2 = amp[b | o2], a3 = amp[b | o1 | o2];
+        double2 r[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (REAL) {
+                double re = M.m[4 * i].x * a0.x, im = M.m[4 * i].x * a0.y;
+                re = fma(M.m[4 * i + 1].x, a1.x, re); im = fma(M.m[4 * i + 1].x, a1.y, im);
+                re = fma(M.m[4 * i + 2].x, a2.x, re); im = fma(M.m[4 * i + 2].x, a2.y, im);
+                re = fma(M.m[4 * i + 3].x, a3.x, re); im = fma(M.m[4 * i + 3].x, a3.y, im);
+                r[i] = make_double2(re, im);
+            } else {
+                double2 acc = cmul(M.m[4 * i], a0);
+                acc = cfma(M.m[4 * i + 1], a1, acc);
+                acc = cfma(M.m[4 * i + 2], a2, acc);
+                acc = cfma(M.m[4 * i + 3], a3, acc);
+                r[i] = acc;
+            }
+        }
+        amp[b] = r[0];
+        amp[b | o1] = r[1];
+        amp[b | o2] = r[2];
+        amp[b | o1 | o2] = r[3];
+    }
+}
+
 // Generic dense k-qubit gate, 3 <= k <= 12 (user-supplied unitaries, projectors).
 // One CTA per group of 2^k amplitudes: gather to smem, one warp per output row
 // (coalesced matrix reads, shuffle reduction), scatter back.  In place.
@@ -273,13 +334,6 @@ __global__ void __launch_bounds__(256) k_dense_big(double2* __restrict__ amp, in
 }
 
 // ------------------------------------------------------------- host side --
-struct HGate {
-    int k;
-    int q[QSV_MAX_GATE_QUBITS];  // physical bit of matrix index bit j
-    std::vector<cplx> m;         // 2^k x 2^k row-major (dense / mono) or 2^k (diag)
-    bool diag;
-};
-
 static bool mat_is_diag(const std::vector<cplx>& m, int dim) {
     for (int r = 0; r < dim; ++r)
         for (int c = 0; c < dim; ++c)
@@ -566,8 +620,7 @@ static int apply_dense_big(qsv_state* s, const HGate& g) {
 
 // Build the device ops of one pass into the staging area (no launch).
 static int build_pass(qsv_state* s, const std::vector<HGate>& gates, const PassPlan& plan, int T,
-                      char* stage, size_t stage_cap, size_t& stage_used, char* dev_base,
-                      PassParams& P) {
+                      std::vector<char>& stage, PassParams& P, size_t& ops_off, size_t& data_off) {
     const int n = s->n_local;
     const int cap = std::min(T, n);
     uint64_t active = plan.qmask;
@@ -657,17 +710,45 @@ static int build_pass(qsv_state* s, const std::vector<HGate>& gates, const PassP
         }
         ++gi;
     }
-    size_t ops_bytes = ops.size() * sizeof(DevOp);
-    size_t data_bytes = data.size() * sizeof(double2);
-    size_t off = (stage_used + 15) & ~(size_t)15;
-    if (off + ops_bytes + data_bytes > stage_cap)
-        QSV_FAIL(QSV_ERR_UNSUPPORTED, "internal: op staging overflow");
-    memcpy(stage + off, ops.data(), ops_bytes);
-    memcpy(stage + off + ops_bytes, data.data(), data_bytes);
+    const size_t ops_bytes = ops.size() * sizeof(DevOp);
+    const size_t data_bytes = data.size() * sizeof(double2);
+    ops_off = (stage.size() + 15) & ~(size_t)15;
+    data_off = ops_off + ops_bytes;
+    stage.resize(data_off + data_bytes);
+    memcpy(stage.data() + ops_off, ops.data(), ops_bytes);
+    memcpy(stage.data() + data_off, data.data(), data_bytes);
     P.nops = (int)ops.size();
-    P.ops = (const DevOp*)(dev_base + off);
-    P.data = (const double2*)(dev_base + off + ops_bytes);
-    stage_used = off + ops_bytes + data_bytes;
+    return QSV_OK;
+}
+
+static bool direct_capable(const HGate& g) {
+    if (g.diag || g.k < 1 || g.k > 2) return false;
+    int src[4];
+    return !mat_is_mono(g.m, 1 << g.k, src);
+}
+
+static int launch_direct(qsv_state* s, const HGate& g) {
+    const bool real = mat_is_real(g.m);
+    const uint64_t groups = qsv_local_size(s) >> g.k;
+    uint64_t blocks = (groups + 255) / 256;
+    const uint64_t cap = (uint64_t)s->num_sms * 16;
+    if (blocks > cap) blocks = cap;
+    if (g.k == 1) {
+        Mat2 M;
+        for (int i = 0; i < 4; ++i) M.m[i] = make_double2(g.m[i].real(), g.m[i].imag());
+        if (real) k_direct1<true><<<(unsigned)blocks, 256, 0, s->stream>>>(s->amp, groups, g.q[0], M);
+        else k_direct1<false><<<(unsigned)blocks, 256, 0, s->stream>>>(s->amp, groups, g.q[0], M);
+    } else {
+        Mat4 M;
+        for (int i = 0; i < 16; ++i) M.m[i] = make_double2(g.m[i].real(), g.m[i].imag());
+        const int lo = std::min(g.q[0], g.q[1]), hi = std::max(g.q[0], g.q[1]);
+        const uint64_t o1 = 1ull << g.q[0], o2 = 1ull << g.q[1];
+        if (real) k_direct2<true><<<(unsigned)blocks, 256, 0, s->stream>>>(s->amp, groups, lo, hi, o1, o2, M);
+        else k_direct2<false><<<(unsigned)blocks, 256, 0, s->stream>>>(s->amp, groups, lo, hi, o1, o2, M);
+    }
+    QSV_CUDA(cudaGetLastError());
+    s->ctr.kernel_launches++;
+    s->ctr.state_passes++;
     return QSV_OK;
 }
 
@@ -691,21 +772,30 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
             std::vector<PassPlan> passes;
             const int T = s->tile_bits;
             plan_passes(seg, s->n_local, T, s->low_bits, no_fusion, passes);
-            size_t cap = 4096;
-            for (const HGate& g : seg) cap += sizeof(DevOp) + 32 + g.m.size() * 16;
-            cap += passes.size() * (((size_t)16 << DIAG_MAX_BITS) + 64);
-            QSV_TRY(qsv_ensure_scratch(s, cap));
-            QSV_TRY(qsv_ensure_pinned(s, cap));
+            std::vector<PassParams> params(passes.size());
+            std::vector<size_t> ops_off(passes.size()), data_off(passes.size());
+            std::vector<char> stage;
+            for (size_t i = 0; i < passes.size(); ++i)
+                QSV_TRY(build_pass(s, seg, passes[i], T, stage, params[i], ops_off[i], data_off[i]));
+            const size_t used = stage.size();
+            QSV_TRY(qsv_ensure_scratch(s, used + 256));
+            QSV_TRY(qsv_ensure_pinned(s, used + 256));
             // the pinned staging area and the device op buffer are reused across calls
             QSV_CUDA(cudaStreamSynchronize(s->stream));
-            std::vector<PassParams> params(passes.size());
-            size_t used = 0;
-            for (size_t i = 0; i < passes.size(); ++i)
-                QSV_TRY(build_pass(s, seg, passes[i], T, (char*)s->pinned, cap, used,
-                                   (char*)s->scratch, params[i]));
+            memcpy(s->pinned, stage.data(), used);
+            for (size_t i = 0; i < passes.size(); ++i) {
+                params[i].ops = (const DevOp*)((char*)s->scratch + ops_off[i]);
+                params[i].data = (const double2*)((char*)s->scratch + data_off[i]);
+            }
             QSV_CUDA(cudaMemcpyAsync(s->scratch, s->pinned, used, cudaMemcpyHostToDevice, s->stream));
-            for (size_t i = 0; i < passes.size(); ++i)
-                QSV_TRY(launch_tile_pass(s, params[i], 1ull << (s->n_local - params[i].T)));
+            s->ctr.h2d_bytes += used;
+            for (size_t i = 0; i < passes.size(); ++i) {
+                if (s->use_direct && passes[i].gate_ids.size() == 1 &&
+                    direct_capable(seg[passes[i].gate_ids[0]]))
+                    QSV_TRY(launch_direct(s, seg[passes[i].gate_ids[0]]));
+                else
+                    QSV_TRY(launch_tile_pass(s, params[i], 1ull << (s->n_local - params[i].T)));
+            }
         }
         if (end < gates.size()) {
             QSV_TRY(apply_dense_big(s, gates[end]));

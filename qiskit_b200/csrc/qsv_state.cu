@@ -69,7 +69,7 @@ static int env_int(const char* name, int dflt) {
     return v && *v ? atoi(v) : dflt;
 }
 
-int qsv_state_alloc(qsv_state** out, int n_qubits, int n_local, int device) {
+int qsv_state_alloc(qsv_state** out, int n_qubits, int n_local, int device, cudaStream_t share_stream) {
     if (!out) QSV_FAIL(QSV_ERR_INVALID, "qsv_create: out is NULL");
     *out = nullptr;
     if (n_qubits < 0) QSV_FAIL(QSV_ERR_INVALID, "qsv_create: n_qubits = %d < 0", n_qubits);
@@ -103,7 +103,13 @@ int qsv_state_alloc(qsv_state** out, int n_qubits, int n_local, int device) {
         delete s;
         QSV_FAIL(QSV_ERR_NOMEM, "qsv_create: cudaMalloc(%zu) failed: %s", need, cudaGetErrorString(e));
     }
-    QSV_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    if (share_stream) {
+        s->stream = share_stream;
+        s->owns_stream = 0;
+    } else {
+        QSV_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+        s->owns_stream = 1;
+    }
     QSV_CUDA(cudaEventCreate(&s->ev0));
     QSV_CUDA(cudaEventCreate(&s->ev1));
     cudaDeviceProp prop;
@@ -118,7 +124,7 @@ int qsv_state_alloc(qsv_state** out, int n_qubits, int n_local, int device) {
 }
 
 extern "C" int qsv_create(qsv_state** out, int n_qubits, int device) {
-    QSV_TRY(qsv_state_alloc(out, n_qubits, n_qubits, device));
+    QSV_TRY(qsv_state_alloc(out, n_qubits, n_qubits, device, nullptr));
     return qsv_init_basis(*out, 0);
 }
 
@@ -129,13 +135,17 @@ extern "C" int qsv_destroy(qsv_state* s) {
     cudaSetDevice(s->device);
     cudaStreamSynchronize(s->stream);
     if (s->dist) qsv_dist_free(s);
+    if (s->aux) {
+        qsv_destroy(s->aux);
+        s->aux = nullptr;
+    }
     if (s->amp) cudaFree(s->amp);
     if (s->scratch) cudaFree(s->scratch);
     if (s->flush_buf) cudaFree(s->flush_buf);
     if (s->pinned) cudaFreeHost(s->pinned);
     cudaEventDestroy(s->ev0);
     cudaEventDestroy(s->ev1);
-    cudaStreamDestroy(s->stream);
+    if (s->owns_stream) cudaStreamDestroy(s->stream);
     delete s;
     return QSV_OK;
 }
@@ -143,7 +153,7 @@ extern "C" int qsv_destroy(qsv_state* s) {
 extern "C" int qsv_clone(const qsv_state* s, qsv_state** out) {
     if (!s) QSV_FAIL(QSV_ERR_INVALID, "qsv_clone: state is NULL");
     if (s->world != 1) QSV_FAIL(QSV_ERR_UNSUPPORTED, "qsv_clone: sharded states cannot be cloned");
-    QSV_TRY(qsv_state_alloc(out, s->n, s->n_local, s->device));
+    QSV_TRY(qsv_state_alloc(out, s->n, s->n_local, s->device, nullptr));
     qsv_state* c = *out;
     c->tile_bits = s->tile_bits;
     c->low_bits = s->low_bits;

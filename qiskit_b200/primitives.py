@@ -223,7 +223,7 @@ def _observables_array(observables, num_qubits: int) -> np.ndarray:
         raise ValueError("ragged observables array")
     out = np.empty((len(subs),) + subs[0].shape, dtype=object)
     for i, s in enumerate(subs):
-        out[i] = s
+        out[i] = s[()] if s.ndim == 0 else s   # a 0-d object array would be stored as-is
     return out
 
 

@@ -262,6 +262,35 @@ def test_expval_heisenberg_and_tfim_ops():
         assert abs(sv.expectation_value(op) - want) < ATOL
 
 
+@pytest.mark.parametrize("n", [8, 9, 14])
+def test_expval_many_z_terms_and_qwc_families(n):
+    """> 512 Z-type terms (several WHT launches) and X/Y/Z families large enough to take the
+    basis-change route, mixed with stray terms that stay on the direct route."""
+    rng = np.random.default_rng(n)
+    psi = random_state(n, 3 * n)
+    sv = Statevector(psi)
+    from qiskit_b200.pauli import PauliList
+    z = rng.integers(2, size=(700, n)).astype(bool)
+    op = SparsePauliOp(PauliList(z, np.zeros_like(z)), rng.standard_normal(700))
+    want = ref.expectation_value_sparse(psi, op.paulis.z, op.paulis.x, op.coeffs)
+    assert abs(sv.expectation_value(op) - want) < ATOL
+    labels = []
+    for basis in "XYZ":
+        for _ in range(40):
+            supp = rng.integers(2, size=n).astype(bool)
+            labels.append("".join(basis if b else "I" for b in supp))
+    for _ in range(30):      # mixed families: X on even qubits, Z on odd
+        supp = rng.integers(2, size=n).astype(bool)
+        labels.append("".join(("X" if q % 2 == 0 else "Z") if supp[q] else "I" for q in range(n)))
+    labels += ["".join(rng.choice(list("IXYZ"), size=n)) for _ in range(20)]
+    op = SparsePauliOp(labels, rng.standard_normal(len(labels)) + 1j * rng.standard_normal(len(labels)))
+    want = ref.expectation_value_sparse(psi, op.paulis.z, op.paulis.x, op.coeffs)
+    before = sv.counters()["read_passes"]
+    assert abs(sv.expectation_value(op) - want) < ATOL
+    assert sv.counters()["read_passes"] - before < len(labels) // 2     # batched, not per term
+    np.testing.assert_array_equal(sv.data, psi)                          # the state is untouched
+
+
 def test_expval_generic_operator_and_inner():
     psi = random_state(4, 5)
     m = random_unitary(2, np.random.default_rng(1))
@@ -480,7 +509,7 @@ def test_estimator_reset_trajectories_reproducible():
     a = StatevectorEstimator(seed=12).run([(qc, ["Z", "X"], [[0.3]])]).result()[0].data.evs
     b = StatevectorEstimator(seed=12).run([(qc, ["Z", "X"], [[0.3]])]).result()[0].data.evs
     np.testing.assert_array_equal(a, b)
-    np.testing.assert_allclose(a, [[np.cos(0.3)], [np.sin(0.3)]], atol=1e-12)
+    np.testing.assert_allclose(a, [np.cos(0.3), np.sin(0.3)], atol=1e-12)
 
 
 # -------------------------------------------------------- A12: sampler ------
