@@ -71,6 +71,9 @@ typedef struct qsv_counters {
     uint64_t gates_applied;   /* gates received through the API (before fusion) */
     uint64_t h2d_bytes;
     uint64_t d2h_bytes;
+    uint64_t phases;          /* register-cluster phases executed inside fused passes */
+    uint64_t swap_count;      /* sharded states: global<->local qubit exchanges */
+    uint64_t swap_bytes;      /* bytes this rank sent over NVLink in those exchanges */
 } qsv_counters;
 
 /* ---- library ---------------------------------------------------------- */

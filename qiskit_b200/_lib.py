@@ -42,6 +42,9 @@ class QsvCounters(C.Structure):
         ("gates_applied", C.c_uint64),
         ("h2d_bytes", C.c_uint64),
         ("d2h_bytes", C.c_uint64),
+        ("phases", C.c_uint64),
+        ("swap_count", C.c_uint64),
+        ("swap_bytes", C.c_uint64),
     ]
 
 

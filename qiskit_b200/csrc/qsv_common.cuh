@@ -63,6 +63,7 @@ struct qsv_state {
     int low_bits;   // L: lowest L index bits are always part of a tile (coalescing)
     int tile_threads;
     int use_direct;  // use register-resident kernels for single-gate passes
+    int use_cluster; // fused passes through k_cluster_pass (register phases) instead of k_tile_pass
     int num_sms;
     qsv_counters ctr;
     // sharding

@@ -426,6 +426,7 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
             aux->low_bits = s->low_bits;
             aux->tile_threads = s->tile_threads;
             aux->use_direct = s->use_direct;
+            aux->use_cluster = s->use_cluster;
             s->aux = aux;
         } else if (rc == QSV_ERR_NOMEM) {
             for (QwcGroup* g : rotated) direct.insert(direct.end(), g->members.begin(), g->members.end());

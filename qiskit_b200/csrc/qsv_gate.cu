@@ -230,6 +230,271 @@ __global__ void __launch_bounds__(NT, 512 / NT) k_tile_pass(double2* __restrict_
     }
 }
 
+// ---- cluster pass: the fused-pass kernel ---------------------------------------------------
+// k_tile_pass above sweeps the whole tile through shared memory once per gate; ncu shows it
+// bound by shared-memory wavefronts and barriers (profiles/r1_ncu_tile.txt).  Here a pass is
+// cut into PHASES.  In a phase every thread owns the 2^4 amplitudes that differ in four
+// "register bits" of the tile index and applies every gate of the phase that acts inside
+// those bits without touching shared memory; diagonal gates act on any bits.  Between
+// phases the tile is re-dealt through shared memory (one write + one read per amplitude).
+// Shared-memory slots are XOR-swizzled so that both the coalesced global<->shared copy and the
+// per-phase gathers are free of bank conflicts (host picks the lane bits accordingly).
+#define CL_R 4
+#define CL_REGS (1 << CL_R)
+enum { CL_DENSE1 = 0, CL_DENSE1R = 1, CL_DENSE2 = 2, CL_DENSE2R = 3, CL_DIAG = 4, CL_MONO = 5 };
+
+struct ClSub {                 // 64 bytes
+    uint8_t kind, k;
+    uint8_t b[3];              // register-bit indices, ascending (dense / mono)
+    uint8_t flags;             // MONO: 1 = all coefficients are exactly 1
+    uint8_t nbits;             // DIAG: table index bits
+    int8_t bits[10];           // DIAG: tile bit feeding table index bit j
+    uint8_t pad0[3];
+    uint32_t data_off;         // into the pass data buffer, double2 units
+    uint32_t aux;              // MONO: source row of output row r at bits [3r, 3r+3)
+    uint16_t regpart[CL_REGS]; // DIAG: table index contribution of register r
+    uint32_t pad1[1];
+};
+static_assert(sizeof(ClSub) == 64, "ClSub layout");
+
+struct ClPhase {               // 16 bytes
+    int8_t rpos[CL_R];         // tile bit of register bit j (ascending)
+    int8_t tpos[9];            // tile bit of thread-index bit j
+    uint8_t nsub;
+    uint16_t sub_first;
+};
+static_assert(sizeof(ClPhase) == 16, "ClPhase layout");
+
+struct ClPass {
+    int T, nphases;
+    int pos[MAX_TILE_BITS];    // ascending global bit position of tile bit b
+    const ClPhase* phases;
+    const ClSub* subs;
+    const double2* data;
+};
+
+__host__ __device__ __forceinline__ uint32_t cl_swz(uint32_t i) {
+    return i ^ (((i >> 3) ^ (i >> 6) ^ (i >> 9) ^ (i >> 12)) & 7u);
+}
+
+// matrix entry load that the compiler may not hoist or keep live across groups (register budget)
+__device__ __forceinline__ double2 cl_ld(const double2* p) {
+    double2 r;
+    asm volatile("ld.global.nc.v2.f64 {%0, %1}, [%2];" : "=d"(r.x), "=d"(r.y) : "l"(p));
+    return r;
+}
+
+template <int B>
+__device__ __forceinline__ void cl_dense1(double2 (&v)[CL_REGS], const double2* __restrict__ m, bool real) {
+    const double2 m00 = __ldg(m), m01 = __ldg(m + 1), m10 = __ldg(m + 2), m11 = __ldg(m + 3);
+#pragma unroll
+    for (int i = 0; i < CL_REGS; ++i) {
+        if (i & (1 << B)) continue;
+        const double2 a0 = v[i], a1 = v[i | (1 << B)];
+        if (real) {
+            v[i] = make_double2(fma(m00.x, a0.x, m01.x * a1.x), fma(m00.x, a0.y, m01.x * a1.y));
+            v[i | (1 << B)] = make_double2(fma(m10.x, a0.x, m11.x * a1.x), fma(m10.x, a0.y, m11.x * a1.y));
+        } else {
+            v[i] = cfma(m01, a1, cmul(m00, a0));
+            v[i | (1 << B)] = cfma(m11, a1, cmul(m10, a0));
+        }
+    }
+}
+
+template <int B0, int B1>
+__device__ __forceinline__ void cl_dense2(double2 (&v)[CL_REGS], const double2* __restrict__ m, bool real) {
+#pragma unroll
+    for (int i = 0; i < CL_REGS; ++i) {
+        if (i & ((1 << B0) | (1 << B1))) continue;
+        const double2 a0 = v[i], a1 = v[i | (1 << B0)], a2 = v[i | (1 << B1)],
+                      a3 = v[i | (1 << B0) | (1 << B1)];
+        double2 o[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const double2 c0 = cl_ld(m + 4 * r), c1 = cl_ld(m + 4 * r + 1), c2 = cl_ld(m + 4 * r + 2),
+                          c3 = cl_ld(m + 4 * r + 3);
+            if (real) {
+                double re = c0.x * a0.x, im = c0.x * a0.y;
+                re = fma(c1.x, a1.x, re); im = fma(c1.x, a1.y, im);
+                re = fma(c2.x, a2.x, re); im = fma(c2.x, a2.y, im);
+                re = fma(c3.x, a3.x, re); im = fma(c3.x, a3.y, im);
+                o[r] = make_double2(re, im);
+            } else {
+                o[r] = cfma(c3, a3, cfma(c2, a2, cfma(c1, a1, cmul(c0, a0))));
+            }
+        }
+        v[i] = o[0];
+        v[i | (1 << B0)] = o[1];
+        v[i | (1 << B1)] = o[2];
+        v[i | (1 << B0) | (1 << B1)] = o[3];
+    }
+}
+
+// generalised permutation on K register bits: out[r] = coef[r] * in[src[r]]
+template <int K, int B0, int B1, int B2>
+__device__ __forceinline__ void cl_mono(double2 (&v)[CL_REGS], uint32_t aux, const double2* __restrict__ coef,
+                                        bool unit) {
+    constexpr int DIM = 1 << K;
+    constexpr int MASK = (1 << B0) | (K > 1 ? (1 << B1) : 0) | (K > 2 ? (1 << B2) : 0);
+#pragma unroll
+    for (int i = 0; i < CL_REGS; ++i) {
+        if (i & MASK) continue;
+        double2 in[DIM], out[DIM];
+#pragma unroll
+        for (int r = 0; r < DIM; ++r)
+            in[r] = v[i | ((r & 1) << B0) | (K > 1 ? ((r >> 1) & 1) << B1 : 0) | (K > 2 ? ((r >> 2) & 1) << B2 : 0)];
+#pragma unroll
+        for (int r = 0; r < DIM; ++r) {
+            const uint32_t src = (aux >> (3 * r)) & 7u;
+            double2 x = in[0];
+#pragma unroll
+            for (int c = 1; c < DIM; ++c)
+                if (src == (uint32_t)c) x = in[c];
+            out[r] = unit ? x : cmul(__ldg(coef + r), x);
+        }
+#pragma unroll
+        for (int r = 0; r < DIM; ++r)
+            v[i | ((r & 1) << B0) | (K > 1 ? ((r >> 1) & 1) << B1 : 0) | (K > 2 ? ((r >> 2) & 1) << B2 : 0)] = out[r];
+    }
+}
+
+__device__ __forceinline__ void cl_apply(double2 (&v)[CL_REGS], const ClSub* __restrict__ sp,
+                                         const double2* __restrict__ data, uint32_t base) {
+    const uint32_t w0 = __ldg(reinterpret_cast<const uint32_t*>(sp));  // kind, k, b0, b1
+    const uint32_t w1 = __ldg(reinterpret_cast<const uint32_t*>(sp) + 1);  // b2, flags, nbits, bits[0]
+    const int kind = w0 & 255, k = (w0 >> 8) & 255, b0 = (w0 >> 16) & 255, b1 = (w0 >> 24) & 255;
+    const int b2 = w1 & 255;
+    const bool unit = (w1 >> 8) & 1;
+    const double2* __restrict__ d = data + __ldg(&sp->data_off);
+#ifndef CL_NO_D1
+    if (kind == CL_DENSE1 || kind == CL_DENSE1R) {
+        const bool real = kind == CL_DENSE1R;
+        switch (b0) {
+            case 0: cl_dense1<0>(v, d, real); break;
+            case 1: cl_dense1<1>(v, d, real); break;
+            case 2: cl_dense1<2>(v, d, real); break;
+            default: cl_dense1<3>(v, d, real); break;
+        }
+    } else
+#endif
+#ifndef CL_NO_D2
+    if (kind == CL_DENSE2 || kind == CL_DENSE2R) {
+        const bool real = kind == CL_DENSE2R;
+        switch (b0 * 4 + b1) {
+            case 1: cl_dense2<0, 1>(v, d, real); break;
+            case 2: cl_dense2<0, 2>(v, d, real); break;
+            case 3: cl_dense2<0, 3>(v, d, real); break;
+            case 6: cl_dense2<1, 2>(v, d, real); break;
+            case 7: cl_dense2<1, 3>(v, d, real); break;
+            default: cl_dense2<2, 3>(v, d, real); break;
+        }
+    } else
+#endif
+#ifndef CL_NO_DIAG
+    if (kind == CL_DIAG) {
+        const int nb = (w1 >> 16) & 255;
+        uint32_t thr = 0;
+        for (int j = 0; j < nb; ++j) thr |= ((base >> sp->bits[j]) & 1u) << j;
+#pragma unroll
+        for (int r = 0; r < CL_REGS; ++r) v[r] = cmul(v[r], __ldg(d + (thr | sp->regpart[r])));
+    } else
+#endif
+    {
+#ifndef CL_NO_MONO
+        const uint32_t aux = __ldg(&sp->aux);
+        if (k == 1) {
+            switch (b0) {
+                case 0: cl_mono<1, 0, 0, 0>(v, aux, d, unit); break;
+                case 1: cl_mono<1, 1, 0, 0>(v, aux, d, unit); break;
+                case 2: cl_mono<1, 2, 0, 0>(v, aux, d, unit); break;
+                default: cl_mono<1, 3, 0, 0>(v, aux, d, unit); break;
+            }
+        } else if (k == 2) {
+            switch (b0 * 4 + b1) {
+                case 1: cl_mono<2, 0, 1, 0>(v, aux, d, unit); break;
+                case 2: cl_mono<2, 0, 2, 0>(v, aux, d, unit); break;
+                case 3: cl_mono<2, 0, 3, 0>(v, aux, d, unit); break;
+                case 6: cl_mono<2, 1, 2, 0>(v, aux, d, unit); break;
+                case 7: cl_mono<2, 1, 3, 0>(v, aux, d, unit); break;
+                default: cl_mono<2, 2, 3, 0>(v, aux, d, unit); break;
+            }
+        } else {
+            switch (b0 * 16 + b1 * 4 + b2) {
+                case 6: cl_mono<3, 0, 1, 2>(v, aux, d, unit); break;
+                case 7: cl_mono<3, 0, 1, 3>(v, aux, d, unit); break;
+                case 11: cl_mono<3, 0, 2, 3>(v, aux, d, unit); break;
+                default: cl_mono<3, 1, 2, 3>(v, aux, d, unit); break;
+            }
+        }
+#endif
+    }
+}
+
+// One fused pass.  NT = 2^(T - CL_R) threads; grid = number of tiles; dynamic smem = 16 * 2^T.
+template <int NT>
+__global__ void __launch_bounds__(NT, (NT <= 256 ? 2 : 1)) k_cluster_pass(double2* __restrict__ amp, const ClPass P) {
+    extern __shared__ double2 tile[];
+    constexpr int LOGNT = NT == 64 ? 6 : (NT == 128 ? 7 : (NT == 256 ? 8 : 9));
+    const int T = LOGNT + CL_R;
+    const uint32_t t = threadIdx.x;
+
+    uint64_t gbase = blockIdx.x;
+    for (int b = 0; b < T; ++b) gbase = insert_zero(gbase, P.pos[b]);
+    uint64_t lo_off = 0;
+#pragma unroll
+    for (int b = 0; b < LOGNT; ++b) lo_off |= (uint64_t)((t >> b) & 1u) << P.pos[b];
+    uint64_t hb[CL_R];
+#pragma unroll
+    for (int j = 0; j < CL_R; ++j) hb[j] = 1ull << P.pos[LOGNT + j];
+    double2* __restrict__ g = amp + gbase + lo_off;
+    const uint32_t st = cl_swz(t);
+
+    // global -> shared: element e = t + r * NT of the tile, 16-byte async copies
+#pragma unroll
+    for (int r = 0; r < CL_REGS; ++r) {
+        const uint64_t off = ((r & 1) ? hb[0] : 0) | ((r & 2) ? hb[1] : 0) | ((r & 4) ? hb[2] : 0) | ((r & 8) ? hb[3] : 0);
+        const uint32_t dst = (uint32_t)__cvta_generic_to_shared(tile + (st ^ cl_swz((uint32_t)r << LOGNT)));
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(g + off));
+    }
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
+    __syncthreads();
+
+    for (int p = 0; p < P.nphases; ++p) {
+        const ClPhase* __restrict__ ph = P.phases + p;
+        const uint4 pw = __ldg(reinterpret_cast<const uint4*>(ph));
+        // bytes 0..3 rpos, 4..12 tpos, 13 nsub, 14..15 sub_first
+        uint32_t base = 0;
+#pragma unroll
+        for (int j = 0; j < LOGNT; ++j) {
+            const int byte = 4 + j;
+            const uint32_t word = byte < 8 ? pw.y : (byte < 12 ? pw.z : pw.w);
+            const int tp = (word >> (8 * (byte & 3))) & 255;
+            base |= ((t >> j) & 1u) << tp;
+        }
+        const uint32_t sb = cl_swz(base);
+        uint32_t s[CL_R];
+#pragma unroll
+        for (int j = 0; j < CL_R; ++j) s[j] = cl_swz(1u << ((pw.x >> (8 * j)) & 255));
+        double2 v[CL_REGS];
+#pragma unroll
+        for (int r = 0; r < CL_REGS; ++r)
+            v[r] = tile[sb ^ ((r & 1) ? s[0] : 0) ^ ((r & 2) ? s[1] : 0) ^ ((r & 4) ? s[2] : 0) ^ ((r & 8) ? s[3] : 0)];
+        const int nsub = (pw.w >> 8) & 255;
+        const ClSub* __restrict__ sp = P.subs + (pw.w >> 16);
+        for (int i = 0; i < nsub; ++i) cl_apply(v, sp + i, P.data, base);
+#pragma unroll
+        for (int r = 0; r < CL_REGS; ++r)
+            tile[sb ^ ((r & 1) ? s[0] : 0) ^ ((r & 2) ? s[1] : 0) ^ ((r & 4) ? s[2] : 0) ^ ((r & 8) ? s[3] : 0)] = v[r];
+        __syncthreads();
+    }
+
+#pragma unroll
+    for (int r = 0; r < CL_REGS; ++r) {
+        const uint64_t off = ((r & 1) ? hb[0] : 0) | ((r & 2) ? hb[1] : 0) | ((r & 4) ? hb[2] : 0) | ((r & 8) ? hb[3] : 0);
+        g[off] = tile[st ^ cl_swz((uint32_t)r << LOGNT)];
+    }
+}
+
 // ---- register-resident kernels for a pass that holds a single dense 1- or 2-qubit gate ----
 // No shared-memory staging: each thread loads its 2 or 4 amplitudes, multiplies by the matrix
 // (kernel parameter, so the entries are constant-bank operands of the DFMAs) and stores.
@@ -721,6 +986,249 @@ static int build_pass(qsv_state* s, const std::vector<HGate>& gates, const PassP
     return QSV_OK;
 }
 
+// ---- cluster pass: host side ----------------------------------------------------------------
+struct TileOp {
+    int kind;                  // CL_*
+    int k;                     // qubits (dense / mono) or table bits (diag)
+    int bits[DIAG_MAX_BITS];   // tile-local bit of matrix / table index bit j
+    std::vector<cplx> m;       // dense: 2^k x 2^k; mono: coef[2^k]; diag: table[2^k]
+    int src[8];                // mono
+    bool unit;
+};
+
+// classify the gates of one pass into tile ops (consecutive diagonal gates share one table)
+static int make_tile_ops(const std::vector<HGate>& gates, const PassPlan& plan, const int* local_of,
+                         std::vector<TileOp>& ops) {
+    const std::vector<int>& ids = plan.gate_ids;
+    size_t gi = 0;
+    while (gi < ids.size()) {
+        const HGate& g = gates[ids[gi]];
+        TileOp op;
+        memset(op.bits, 0, sizeof op.bits);
+        memset(op.src, 0, sizeof op.src);
+        op.unit = false;
+        if (g.diag) {
+            uint64_t um = 0;
+            size_t gj = gi;
+            while (gj < ids.size() && gates[ids[gj]].diag) {
+                uint64_t gm = 0;
+                for (int j = 0; j < gates[ids[gj]].k; ++j) gm |= 1ull << gates[ids[gj]].q[j];
+                if (popc64(um | gm) > DIAG_MAX_BITS) break;
+                um |= gm;
+                ++gj;
+            }
+            if (gj == gi) QSV_FAIL(QSV_ERR_UNSUPPORTED, "diagonal gate wider than %d qubits", DIAG_MAX_BITS);
+            int d = 0;
+            int bit_of[64];
+            for (int b = 0; b < 64; ++b)
+                if ((um >> b) & 1ull) {
+                    bit_of[b] = d;
+                    op.bits[d++] = local_of[b];
+                }
+            op.kind = CL_DIAG;
+            op.k = d;
+            op.m.assign((size_t)1 << d, cplx(1.0, 0.0));
+            for (size_t t = gi; t < gj; ++t) {
+                const HGate& h = gates[ids[t]];
+                for (size_t i = 0; i < op.m.size(); ++i) {
+                    int hi = 0;
+                    for (int j = 0; j < h.k; ++j) hi |= (int)((i >> bit_of[h.q[j]]) & 1) << j;
+                    op.m[i] *= h.m[hi];
+                }
+            }
+            ops.push_back(std::move(op));
+            gi = gj;
+            continue;
+        }
+        const int dim = 1 << g.k;
+        for (int j = 0; j < g.k && j < DIAG_MAX_BITS; ++j) op.bits[j] = local_of[g.q[j]];
+        op.k = g.k;
+        if (g.k <= 3 && mat_is_mono(g.m, dim, op.src)) {
+            op.kind = CL_MONO;
+            op.unit = true;
+            op.m.resize(dim);
+            for (int r = 0; r < dim; ++r) {
+                op.m[r] = g.m[(size_t)r * dim + op.src[r]];
+                op.unit &= (op.m[r] == cplx(1.0, 0.0));
+            }
+        } else if (g.k == 1 || g.k == 2) {
+            const bool real = mat_is_real(g.m);
+            op.kind = g.k == 1 ? (real ? CL_DENSE1R : CL_DENSE1) : (real ? CL_DENSE2R : CL_DENSE2);
+            op.m = g.m;
+        } else {
+            QSV_FAIL(QSV_ERR_UNSUPPORTED, "internal: dense %d-qubit gate reached the tile path", g.k);
+        }
+        ops.push_back(std::move(op));
+        ++gi;
+    }
+    return QSV_OK;
+}
+
+static inline int rank_in(uint32_t set, int bit) { return __builtin_popcount(set & ((1u << bit) - 1u)); }
+
+// Build phases / sub-ops / data of one cluster pass into the staging area (no launch).
+static int build_cluster_pass(qsv_state* s, const std::vector<HGate>& gates, const PassPlan& plan, int T,
+                              std::vector<char>& stage, ClPass& P, size_t& phases_off, size_t& subs_off,
+                              size_t& data_off) {
+    const int n = s->n_local;
+    const int cap = std::min(T, n);
+    uint64_t active = plan.qmask;
+    for (int b = 0; b < n && popc64(active) < cap; ++b) active |= 1ull << b;  // low bits first
+    memset(&P, 0, sizeof P);
+    P.T = popc64(active);
+    int local_of[64];
+    for (int b = 0, t = 0; b < 64; ++b) {
+        local_of[b] = -1;
+        if ((active >> b) & 1ull) {
+            P.pos[t] = b;
+            local_of[b] = t++;
+        }
+    }
+    std::vector<TileOp> ops;
+    QSV_TRY(make_tile_ops(gates, plan, local_of, ops));
+
+    std::vector<ClPhase> phases;
+    std::vector<ClSub> subs;
+    std::vector<double2> data;
+    std::vector<char> done(ops.size(), 0);
+    size_t ndone = 0;
+    const int TT = P.T;
+    while (ndone < ops.size()) {
+        uint32_t S = 0, blocked = 0;
+        std::vector<int> sel;
+        for (size_t i = 0; i < ops.size(); ++i) {
+            if (done[i]) continue;
+            uint32_t m = 0;
+            for (int j = 0; j < ops[i].k; ++j) m |= 1u << ops[i].bits[j];
+            if (m & blocked) {
+                blocked |= m;
+                continue;
+            }
+            if (ops[i].kind != CL_DIAG) {
+                if (__builtin_popcount(S | m) > CL_R) {
+                    blocked |= m;
+                    continue;
+                }
+                S |= m;
+            }
+            sel.push_back((int)i);
+            done[i] = 1;
+            ++ndone;
+        }
+        for (int b = TT - 1; b >= 0 && __builtin_popcount(S) < CL_R; --b) S |= 1u << b;
+        ClPhase ph;
+        memset(&ph, 0, sizeof ph);
+        for (int b = 0, j = 0; b < TT; ++b)
+            if ((S >> b) & 1u) ph.rpos[j++] = (int8_t)b;
+        // thread bits: lanes 0..2 on three non-register tile bits with distinct (bit mod 3), so that
+        // a quarter-warp's 16-byte accesses fall into distinct swizzled slots
+        uint32_t rest = ((1u << TT) - 1u) & ~S;
+        int nt = 0;
+        for (int c = 0; c < 3; ++c)
+            for (int b = 0; b < TT; ++b)
+                if (((rest >> b) & 1u) && b % 3 == c) {
+                    ph.tpos[nt++] = (int8_t)b;
+                    rest &= ~(1u << b);
+                    break;
+                }
+        for (int b = 0; b < TT; ++b)
+            if ((rest >> b) & 1u) ph.tpos[nt++] = (int8_t)b;
+        ph.sub_first = (uint16_t)subs.size();
+        ph.nsub = (uint8_t)sel.size();
+        if (sel.size() > 255 || subs.size() + sel.size() > 65535)
+            QSV_FAIL(QSV_ERR_UNSUPPORTED, "internal: too many ops in one pass");
+        for (int id : sel) {
+            const TileOp& op = ops[id];
+            ClSub sb;
+            memset(&sb, 0, sizeof sb);
+            sb.kind = (uint8_t)op.kind;
+            sb.k = (uint8_t)op.k;
+            sb.data_off = (uint32_t)data.size();
+            if (op.kind == CL_DIAG) {
+                sb.nbits = (uint8_t)op.k;
+                for (int j = 0; j < op.k; ++j) sb.bits[j] = (int8_t)op.bits[j];
+                for (int r = 0; r < CL_REGS; ++r) {
+                    uint32_t roff = 0;
+                    for (int j = 0; j < CL_R; ++j) roff |= (uint32_t)((r >> j) & 1) << ph.rpos[j];
+                    uint32_t part = 0;
+                    for (int j = 0; j < op.k; ++j) part |= ((roff >> op.bits[j]) & 1u) << j;
+                    sb.regpart[r] = (uint16_t)part;
+                }
+                for (const cplx& v : op.m) data.push_back(make_double2(v.real(), v.imag()));
+            } else {
+                // canonical order: register bits ascending; order[j'] = matrix bit feeding canonical bit j'
+                int rb[3], order[3] = {0, 1, 2};
+                for (int j = 0; j < op.k; ++j) rb[j] = rank_in(S, op.bits[j]);
+                std::sort(order, order + op.k, [&](int a, int b) { return rb[a] < rb[b]; });
+                for (int j = 0; j < op.k; ++j) sb.b[j] = (uint8_t)rb[order[j]];
+                const int dim = 1 << op.k;
+                auto to_orig = [&](int rc) {
+                    int r = 0;
+                    for (int j = 0; j < op.k; ++j) r |= ((rc >> j) & 1) << order[j];
+                    return r;
+                };
+                auto to_canon = [&](int r) {
+                    int rc = 0;
+                    for (int j = 0; j < op.k; ++j) rc |= ((r >> order[j]) & 1) << j;
+                    return rc;
+                };
+                if (op.kind == CL_MONO) {
+                    sb.flags = op.unit ? 1 : 0;
+                    for (int rc = 0; rc < dim; ++rc) {
+                        const int r = to_orig(rc);
+                        sb.aux |= (uint32_t)to_canon(op.src[r]) << (3 * rc);
+                        data.push_back(make_double2(op.m[r].real(), op.m[r].imag()));
+                    }
+                } else {
+                    for (int rc = 0; rc < dim; ++rc)
+                        for (int cc = 0; cc < dim; ++cc) {
+                            const cplx v = op.m[(size_t)to_orig(rc) * dim + to_orig(cc)];
+                            data.push_back(make_double2(v.real(), v.imag()));
+                        }
+                }
+            }
+            subs.push_back(sb);
+        }
+        phases.push_back(ph);
+    }
+    const size_t ph_bytes = phases.size() * sizeof(ClPhase);
+    const size_t sub_bytes = subs.size() * sizeof(ClSub);
+    const size_t data_bytes = data.size() * sizeof(double2);
+    phases_off = (stage.size() + 63) & ~(size_t)63;
+    subs_off = (phases_off + ph_bytes + 63) & ~(size_t)63;
+    data_off = (subs_off + sub_bytes + 15) & ~(size_t)15;
+    stage.resize(data_off + data_bytes);
+    memcpy(stage.data() + phases_off, phases.data(), ph_bytes);
+    memcpy(stage.data() + subs_off, subs.data(), sub_bytes);
+    memcpy(stage.data() + data_off, data.data(), data_bytes);
+    P.nphases = (int)phases.size();
+    s->ctr.phases += phases.size();
+    return QSV_OK;
+}
+
+template <int NT>
+static int launch_cluster_nt(qsv_state* s, const ClPass& P, uint64_t ntiles) {
+    const size_t smem = (size_t)16 << P.T;
+    QSV_CUDA(cudaFuncSetAttribute(k_cluster_pass<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_cluster_pass<NT><<<(unsigned)ntiles, NT, smem, s->stream>>>(s->amp, P);
+    return QSV_OK;
+}
+
+static int launch_cluster_pass(qsv_state* s, const ClPass& P, uint64_t ntiles) {
+    if (ntiles > 0x7fffffffull) QSV_FAIL(QSV_ERR_UNSUPPORTED, "too many tiles for one launch");
+    switch (P.T) {
+        case 10: QSV_TRY(launch_cluster_nt<64>(s, P, ntiles)); break;
+        case 11: QSV_TRY(launch_cluster_nt<128>(s, P, ntiles)); break;
+        case 12: QSV_TRY(launch_cluster_nt<256>(s, P, ntiles)); break;
+        case 13: QSV_TRY(launch_cluster_nt<512>(s, P, ntiles)); break;
+        default: QSV_FAIL(QSV_ERR_UNSUPPORTED, "internal: cluster pass with %d tile bits", P.T);
+    }
+    QSV_CUDA(cudaGetLastError());
+    s->ctr.kernel_launches++;
+    s->ctr.state_passes++;
+    return QSV_OK;
+}
+
 static bool direct_capable(const HGate& g) {
     if (g.diag || g.k < 1 || g.k > 2) return false;
     int src[4];
@@ -773,28 +1281,45 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
             const int T = s->tile_bits;
             plan_passes(seg, s->n_local, T, s->low_bits, no_fusion, passes);
             std::vector<PassParams> params(passes.size());
-            std::vector<size_t> ops_off(passes.size()), data_off(passes.size());
+            std::vector<ClPass> cparams(passes.size());
+            std::vector<size_t> ops_off(passes.size()), data_off(passes.size()), subs_off(passes.size());
+            std::vector<char> kind(passes.size(), 0);  // 0 legacy tile, 1 cluster, 2 direct
             std::vector<char> stage;
-            for (size_t i = 0; i < passes.size(); ++i)
-                QSV_TRY(build_pass(s, seg, passes[i], T, stage, params[i], ops_off[i], data_off[i]));
-            const size_t used = stage.size();
-            QSV_TRY(qsv_ensure_scratch(s, used + 256));
-            QSV_TRY(qsv_ensure_pinned(s, used + 256));
-            // the pinned staging area and the device op buffer are reused across calls
-            QSV_CUDA(cudaStreamSynchronize(s->stream));
-            memcpy(s->pinned, stage.data(), used);
             for (size_t i = 0; i < passes.size(); ++i) {
-                params[i].ops = (const DevOp*)((char*)s->scratch + ops_off[i]);
-                params[i].data = (const double2*)((char*)s->scratch + data_off[i]);
+                if (s->use_direct && passes[i].gate_ids.size() == 1 && direct_capable(seg[passes[i].gate_ids[0]])) {
+                    kind[i] = 2;
+                } else if (s->use_cluster && std::min(T, s->n_local) >= 10) {
+                    kind[i] = 1;
+                    QSV_TRY(build_cluster_pass(s, seg, passes[i], T, stage, cparams[i], ops_off[i], subs_off[i],
+                                               data_off[i]));
+                } else {
+                    QSV_TRY(build_pass(s, seg, passes[i], T, stage, params[i], ops_off[i], data_off[i]));
+                }
             }
-            QSV_CUDA(cudaMemcpyAsync(s->scratch, s->pinned, used, cudaMemcpyHostToDevice, s->stream));
-            s->ctr.h2d_bytes += used;
+            const size_t used = stage.size();
+            if (used) {
+                QSV_TRY(qsv_ensure_scratch(s, used + 256));
+                QSV_TRY(qsv_ensure_pinned(s, used + 256));
+                // the pinned staging area and the device op buffer are reused across calls
+                QSV_CUDA(cudaStreamSynchronize(s->stream));
+                memcpy(s->pinned, stage.data(), used);
+                QSV_CUDA(cudaMemcpyAsync(s->scratch, s->pinned, used, cudaMemcpyHostToDevice, s->stream));
+                s->ctr.h2d_bytes += used;
+            }
             for (size_t i = 0; i < passes.size(); ++i) {
-                if (s->use_direct && passes[i].gate_ids.size() == 1 &&
-                    direct_capable(seg[passes[i].gate_ids[0]]))
+                char* base = (char*)s->scratch;
+                if (kind[i] == 2) {
                     QSV_TRY(launch_direct(s, seg[passes[i].gate_ids[0]]));
-                else
+                } else if (kind[i] == 1) {
+                    cparams[i].phases = (const ClPhase*)(base + ops_off[i]);
+                    cparams[i].subs = (const ClSub*)(base + subs_off[i]);
+                    cparams[i].data = (const double2*)(base + data_off[i]);
+                    QSV_TRY(launch_cluster_pass(s, cparams[i], 1ull << (s->n_local - cparams[i].T)));
+                } else {
+                    params[i].ops = (const DevOp*)(base + ops_off[i]);
+                    params[i].data = (const double2*)(base + data_off[i]);
                     QSV_TRY(launch_tile_pass(s, params[i], 1ull << (s->n_local - params[i].T)));
+                }
             }
         }
         if (end < gates.size()) {

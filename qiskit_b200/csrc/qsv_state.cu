@@ -119,6 +119,7 @@ int qsv_state_alloc(qsv_state** out, int n_qubits, int n_local, int device, cuda
     s->low_bits = env_int("QSV_LOW_BITS", 4);
     s->tile_threads = env_int("QSV_TILE_THREADS", 256);
     s->use_direct = env_int("QSV_USE_DIRECT", 1);
+    s->use_cluster = env_int("QSV_USE_CLUSTER", 1);
     *out = s;
     return QSV_OK;
 }
@@ -159,6 +160,7 @@ extern "C" int qsv_clone(const qsv_state* s, qsv_state** out) {
     c->low_bits = s->low_bits;
     c->tile_threads = s->tile_threads;
     c->use_direct = s->use_direct;
+    c->use_cluster = s->use_cluster;
     QSV_CUDA(cudaStreamSynchronize(s->stream));
     QSV_CUDA(cudaMemcpyAsync(c->amp, s->amp, (size_t)16 << s->n_local, cudaMemcpyDeviceToDevice,
                              c->stream));
@@ -284,6 +286,8 @@ extern "C" int qsv_set_option(qsv_state* s, const char* name, int64_t value) {
         s->tile_threads = (int)value;
     } else if (!strcmp(name, "use_direct")) {
         s->use_direct = value != 0;
+    } else if (!strcmp(name, "use_cluster")) {
+        s->use_cluster = value != 0;
     } else {
         QSV_FAIL(QSV_ERR_INVALID, "qsv_set_option: unknown option '%s'", name);
     }
