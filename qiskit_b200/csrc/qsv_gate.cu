@@ -257,16 +257,25 @@ struct ClSub {                 // 64 bytes
 };
 static_assert(sizeof(ClSub) == 64, "ClSub layout");
 
-struct ClPhase {               // 16 bytes
+#define CL_PERM_ID 0xFEDCBA9876543210ull
+#define CL_NOCOEF 0xffffffffu
+struct ClPhase {               // 48 bytes
     int8_t rpos[CL_R];         // tile bit of register bit j (ascending)
     int8_t tpos[9];            // tile bit of thread-index bit j
     uint8_t nsub;
     uint16_t sub_first;
+    // generalised permutations inside the register bits that open / close the phase are folded
+    // into the shared-memory addresses: register r is READ from slot nibble r of rperm (times
+    // data[rcoef + r]) and register q is WRITTEN to slot nibble q of wperm (times data[wcoef + q])
+    uint32_t rperm_lo, rperm_hi, wperm_lo, wperm_hi;
+    uint32_t rcoef, wcoef;     // CL_NOCOEF = all ones
+    uint32_t pad[2];
 };
-static_assert(sizeof(ClPhase) == 16, "ClPhase layout");
+static_assert(sizeof(ClPhase) == 48, "ClPhase layout");
 
 struct ClPass {
     int T, nphases;
+    uint64_t index_base;       // sharded states: rank << n_local (bits of diagonal gates above the slab)
     int pos[MAX_TILE_BITS];    // ascending global bit position of tile bit b
     const ClPhase* phases;
     const ClSub* subs;
@@ -311,8 +320,8 @@ __device__ __forceinline__ void cl_dense2(double2 (&v)[CL_REGS], const double2* 
         double2 o[4];
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
-            const double2 c0 = cl_ld(m + 4 * r), c1 = cl_ld(m + 4 * r + 1), c2 = cl_ld(m + 4 * r + 2),
-                          c3 = cl_ld(m + 4 * r + 3);
+            const double2 c0 = __ldg(m + 4 * r), c1 = __ldg(m + 4 * r + 1), c2 = __ldg(m + 4 * r + 2),
+                          c3 = __ldg(m + 4 * r + 3);
             if (real) {
                 double re = c0.x * a0.x, im = c0.x * a0.y;
                 re = fma(c1.x, a1.x, re); im = fma(c1.x, a1.y, im);
@@ -359,7 +368,7 @@ __device__ __forceinline__ void cl_mono(double2 (&v)[CL_REGS], uint32_t aux, con
 }
 
 __device__ __forceinline__ void cl_apply(double2 (&v)[CL_REGS], const ClSub* __restrict__ sp,
-                                         const double2* __restrict__ data, uint32_t base) {
+                                         const double2* __restrict__ data, uint32_t base, uint64_t tile_base) {
     const uint32_t w0 = __ldg(reinterpret_cast<const uint32_t*>(sp));  // kind, k, b0, b1
     const uint32_t w1 = __ldg(reinterpret_cast<const uint32_t*>(sp) + 1);  // b2, flags, nbits, bits[0]
     const int kind = w0 & 255, k = (w0 >> 8) & 255, b0 = (w0 >> 16) & 255, b1 = (w0 >> 24) & 255;
@@ -394,7 +403,11 @@ __device__ __forceinline__ void cl_apply(double2 (&v)[CL_REGS], const ClSub* __r
     if (kind == CL_DIAG) {
         const int nb = (w1 >> 16) & 255;
         uint32_t thr = 0;
-        for (int j = 0; j < nb; ++j) thr |= ((base >> sp->bits[j]) & 1u) << j;
+        for (int j = 0; j < nb; ++j) {
+            const int bj = sp->bits[j];  // tile bit, or 64 + global bit for a bit outside the tile
+            const uint32_t bit = bj >= 64 ? (uint32_t)(tile_base >> (bj - 64)) & 1u : (base >> bj) & 1u;
+            thr |= bit << j;
+        }
 #pragma unroll
         for (int r = 0; r < CL_REGS; ++r) v[r] = cmul(v[r], __ldg(d + (thr | sp->regpart[r])));
     } else
@@ -430,29 +443,35 @@ __device__ __forceinline__ void cl_apply(double2 (&v)[CL_REGS], const ClSub* __r
     }
 }
 
-// One fused pass.  NT = 2^(T - CL_R) threads; grid = number of tiles; dynamic smem = 16 * 2^T.
-template <int NT>
-__global__ void __launch_bounds__(NT, (NT <= 256 ? 2 : 1)) k_cluster_pass(double2* __restrict__ amp, const ClPass P) {
+// One fused pass.  Tile = 2^T amplitudes, T = log2(NT) + log2(SETS) + CL_R: NT threads, each
+// owning SETS groups of 16 amplitudes per phase (processed one after the other, so the register
+// budget is that of one group: 254 registers at NT = 128, two CTAs per SM, no spills).
+// Grid = number of tiles; dynamic smem = 16 * 2^T bytes.
+template <int NT, int SETS>
+__global__ void __launch_bounds__(NT, 2) k_cluster_pass(double2* __restrict__ amp, const __grid_constant__ ClPass P) {
     extern __shared__ double2 tile[];
-    constexpr int LOGNT = NT == 64 ? 6 : (NT == 128 ? 7 : (NT == 256 ? 8 : 9));
-    const int T = LOGNT + CL_R;
+    constexpr int LOGNT = NT == 64 ? 6 : 7;
+    constexpr int LOGS = SETS == 1 ? 0 : (SETS == 2 ? 1 : 2);
+    constexpr int LOGV = LOGNT + LOGS;        // tile bits spanned by (thread, set)
+    constexpr int T = LOGV + CL_R;
+    constexpr int NCOPY = CL_REGS * SETS;      // 16-byte elements per thread in the global copies
     const uint32_t t = threadIdx.x;
-
-    uint64_t gbase = blockIdx.x;
-    for (int b = 0; b < T; ++b) gbase = insert_zero(gbase, P.pos[b]);
-    uint64_t lo_off = 0;
-#pragma unroll
-    for (int b = 0; b < LOGNT; ++b) lo_off |= (uint64_t)((t >> b) & 1u) << P.pos[b];
-    uint64_t hb[CL_R];
-#pragma unroll
-    for (int j = 0; j < CL_R; ++j) hb[j] = 1ull << P.pos[LOGNT + j];
-    double2* __restrict__ g = amp + gbase + lo_off;
     const uint32_t st = cl_swz(t);
+    uint64_t tile_base = blockIdx.x;
+    for (int b = 0; b < T; ++b) tile_base = insert_zero(tile_base, P.pos[b]);
+    uint64_t gbase = tile_base;
+#pragma unroll
+    for (int b = 0; b < LOGNT; ++b) gbase |= (uint64_t)((t >> b) & 1u) << P.pos[b];
+    double2* __restrict__ g = amp + gbase;
+    tile_base |= P.index_base;
 
     // global -> shared: element e = t + r * NT of the tile, 16-byte async copies
 #pragma unroll
-    for (int r = 0; r < CL_REGS; ++r) {
-        const uint64_t off = ((r & 1) ? hb[0] : 0) | ((r & 2) ? hb[1] : 0) | ((r & 4) ? hb[2] : 0) | ((r & 8) ? hb[3] : 0);
+    for (int r = 0; r < NCOPY; ++r) {
+        uint64_t off = 0;
+#pragma unroll
+        for (int j = 0; j < T - LOGNT; ++j)
+            if ((r >> j) & 1) off |= 1ull << P.pos[LOGNT + j];
         const uint32_t dst = (uint32_t)__cvta_generic_to_shared(tile + (st ^ cl_swz((uint32_t)r << LOGNT)));
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(g + off));
     }
@@ -460,37 +479,71 @@ __global__ void __launch_bounds__(NT, (NT <= 256 ? 2 : 1)) k_cluster_pass(double
     __syncthreads();
 
     for (int p = 0; p < P.nphases; ++p) {
-        const ClPhase* __restrict__ ph = P.phases + p;
-        const uint4 pw = __ldg(reinterpret_cast<const uint4*>(ph));
-        // bytes 0..3 rpos, 4..12 tpos, 13 nsub, 14..15 sub_first
-        uint32_t base = 0;
-#pragma unroll
-        for (int j = 0; j < LOGNT; ++j) {
-            const int byte = 4 + j;
-            const uint32_t word = byte < 8 ? pw.y : (byte < 12 ? pw.z : pw.w);
-            const int tp = (word >> (8 * (byte & 3))) & 255;
-            base |= ((t >> j) & 1u) << tp;
-        }
-        const uint32_t sb = cl_swz(base);
+        const uint4* __restrict__ ph = reinterpret_cast<const uint4*>(P.phases + p);
+        const uint4 pw = __ldg(ph);       // bytes 0..3 rpos, 4..12 tpos, 13 nsub, 14..15 sub_first
+        const uint4 pq = __ldg(ph + 1);   // rperm, wperm
+        const uint4 pc = __ldg(ph + 2);   // rcoef, wcoef
         uint32_t s[CL_R];
 #pragma unroll
         for (int j = 0; j < CL_R; ++j) s[j] = cl_swz(1u << ((pw.x >> (8 * j)) & 255));
-        double2 v[CL_REGS];
-#pragma unroll
-        for (int r = 0; r < CL_REGS; ++r)
-            v[r] = tile[sb ^ ((r & 1) ? s[0] : 0) ^ ((r & 2) ? s[1] : 0) ^ ((r & 4) ? s[2] : 0) ^ ((r & 8) ? s[3] : 0)];
         const int nsub = (pw.w >> 8) & 255;
         const ClSub* __restrict__ sp = P.subs + (pw.w >> 16);
-        for (int i = 0; i < nsub; ++i) cl_apply(v, sp + i, P.data, base);
+#pragma unroll 1
+        for (int set = 0; set < SETS; ++set) {
+            const uint32_t tv = t | ((uint32_t)set << LOGNT);
+            uint32_t base = 0;
 #pragma unroll
-        for (int r = 0; r < CL_REGS; ++r)
-            tile[sb ^ ((r & 1) ? s[0] : 0) ^ ((r & 2) ? s[1] : 0) ^ ((r & 4) ? s[2] : 0) ^ ((r & 8) ? s[3] : 0)] = v[r];
+            for (int j = 0; j < LOGV; ++j) {
+                const int byte = 4 + j;
+                const uint32_t word = byte < 8 ? pw.y : (byte < 12 ? pw.z : pw.w);
+                const int tp = (word >> (8 * (byte & 3))) & 255;
+                base |= ((tv >> j) & 1u) << tp;
+            }
+            const uint32_t sb = cl_swz(base);
+            double2 v[CL_REGS];
+            if (pq.x == (uint32_t)CL_PERM_ID && pq.y == (uint32_t)(CL_PERM_ID >> 32)) {
+#pragma unroll
+                for (int r = 0; r < CL_REGS; ++r)
+                    v[r] = tile[sb ^ ((r & 1) ? s[0] : 0) ^ ((r & 2) ? s[1] : 0) ^ ((r & 4) ? s[2] : 0) ^ ((r & 8) ? s[3] : 0)];
+            } else {
+#pragma unroll
+                for (int r = 0; r < CL_REGS; ++r) {
+                    const uint32_t q = ((r < 8 ? pq.x : pq.y) >> (4 * (r & 7))) & 15u;
+                    v[r] = tile[sb ^ ((q & 1) ? s[0] : 0) ^ ((q & 2) ? s[1] : 0) ^ ((q & 4) ? s[2] : 0) ^ ((q & 8) ? s[3] : 0)];
+                }
+            }
+            if (pc.x != CL_NOCOEF) {
+                const double2* __restrict__ c = P.data + pc.x;
+#pragma unroll
+                for (int r = 0; r < CL_REGS; ++r) v[r] = cmul(__ldg(c + r), v[r]);
+            }
+            for (int i = 0; i < nsub; ++i) cl_apply(v, sp + i, P.data, base, tile_base);
+            if (pc.y != CL_NOCOEF) {
+                const double2* __restrict__ c = P.data + pc.y;
+#pragma unroll
+                for (int r = 0; r < CL_REGS; ++r) v[r] = cmul(__ldg(c + r), v[r]);
+            }
+            if (pq.z == (uint32_t)CL_PERM_ID && pq.w == (uint32_t)(CL_PERM_ID >> 32)) {
+#pragma unroll
+                for (int r = 0; r < CL_REGS; ++r)
+                    tile[sb ^ ((r & 1) ? s[0] : 0) ^ ((r & 2) ? s[1] : 0) ^ ((r & 4) ? s[2] : 0) ^ ((r & 8) ? s[3] : 0)] = v[r];
+            } else {
+#pragma unroll
+                for (int r = 0; r < CL_REGS; ++r) {
+                    const uint32_t q = ((r < 8 ? pq.z : pq.w) >> (4 * (r & 7))) & 15u;
+                    tile[sb ^ ((q & 1) ? s[0] : 0) ^ ((q & 2) ? s[1] : 0) ^ ((q & 4) ? s[2] : 0) ^ ((q & 8) ? s[3] : 0)] = v[r];
+                }
+            }
+        }
         __syncthreads();
     }
 
 #pragma unroll
-    for (int r = 0; r < CL_REGS; ++r) {
-        const uint64_t off = ((r & 1) ? hb[0] : 0) | ((r & 2) ? hb[1] : 0) | ((r & 4) ? hb[2] : 0) | ((r & 8) ? hb[3] : 0);
+    for (int r = 0; r < NCOPY; ++r) {
+        uint64_t off = 0;
+#pragma unroll
+        for (int j = 0; j < T - LOGNT; ++j)
+            if ((r >> j) & 1) off |= 1ull << P.pos[LOGNT + j];
         g[off] = tile[st ^ cl_swz((uint32_t)r << LOGNT)];
     }
 }
@@ -785,7 +838,7 @@ static int popc64(uint64_t v) { return __builtin_popcountll(v); }
 // not blocked by an earlier gate that was left for later, and the pass still
 // fits in T bits together with the forced low bits.
 static void plan_passes(const std::vector<HGate>& gates, int n_local, int T, int L, bool no_fusion,
-                        std::vector<PassPlan>& passes) {
+                        bool free_diag, std::vector<PassPlan>& passes) {
     const size_t G = gates.size();
     std::vector<char> done(G, 0);
     size_t first = 0;
@@ -804,14 +857,17 @@ static void plan_passes(const std::vector<HGate>& gates, int n_local, int T, int
             uint64_t gm = 0;
             for (int j = 0; j < gates[i].k; ++j) gm |= 1ull << gates[i].q[j];
             bool ok = !(gm & blocked);
+            // the cluster kernel reads the bits of a diagonal gate from the tile's position when
+            // they are not tile bits: diagonal gates never claim tile bits
+            const uint64_t tm = (free_diag && gates[i].diag) ? 0ull : gm;
             if (ok) {
-                uint64_t u = p.qmask | gm;
+                uint64_t u = p.qmask | tm;
                 int need = popc64((u | lowmask) & all);
                 if (need > cap) ok = false;
                 if (no_fusion && !p.gate_ids.empty()) ok = false;
             }
             if (ok) {
-                p.qmask |= gm;
+                p.qmask |= tm;
                 p.gate_ids.push_back((int)i);
                 done[i] = 1;
             } else {
@@ -1023,7 +1079,7 @@ static int make_tile_ops(const std::vector<HGate>& gates, const PassPlan& plan, 
             for (int b = 0; b < 64; ++b)
                 if ((um >> b) & 1ull) {
                     bit_of[b] = d;
-                    op.bits[d++] = local_of[b];
+                    op.bits[d++] = local_of[b] >= 0 ? local_of[b] : 64 + b;  // 64 + global bit: outside the tile
                 }
             op.kind = CL_DIAG;
             op.k = d;
@@ -1099,7 +1155,8 @@ static int build_cluster_pass(qsv_state* s, const std::vector<HGate>& gates, con
         for (size_t i = 0; i < ops.size(); ++i) {
             if (done[i]) continue;
             uint32_t m = 0;
-            for (int j = 0; j < ops[i].k; ++j) m |= 1u << ops[i].bits[j];
+            for (int j = 0; j < ops[i].k; ++j)
+                if (ops[i].bits[j] < 64) m |= 1u << ops[i].bits[j];
             if (m & blocked) {
                 blocked |= m;
                 continue;
@@ -1133,11 +1190,102 @@ static int build_cluster_pass(qsv_state* s, const std::vector<HGate>& gates, con
                 }
         for (int b = 0; b < TT; ++b)
             if ((rest >> b) & 1u) ph.tpos[nt++] = (int8_t)b;
+        // Generalised permutations that can be moved to the end (start) of the phase -- they act on
+        // bits no later (earlier) remaining op touches -- are composed into one permutation of the
+        // 16 register slots and folded into the shared-memory write (read) addresses.
+        std::vector<char> role(sel.size(), 0);  // 0 in-register, 1 leading, 2 trailing
+        auto op_mask = [&](int id) {
+            uint32_t m = 0;
+            for (int j = 0; j < ops[id].k; ++j)
+                if (ops[id].bits[j] < 64) m |= 1u << ops[id].bits[j];
+            return m;
+        };
+        {
+            uint32_t blk = 0;
+            for (size_t i = sel.size(); i-- > 0;) {
+                const uint32_t m = op_mask(sel[i]);
+                if (ops[sel[i]].kind == CL_MONO && !(m & blk)) role[i] = 2;
+                else blk |= m;
+            }
+            blk = 0;
+            for (size_t i = 0; i < sel.size(); ++i) {
+                if (role[i]) continue;
+                const uint32_t m = op_mask(sel[i]);
+                if (ops[sel[i]].kind == CL_MONO && !(m & blk)) role[i] = 1;
+                else blk |= m;
+            }
+        }
+        auto compose = [&](int which, int* src16, cplx* c16) {
+            bool any = false;
+            for (int r = 0; r < CL_REGS; ++r) {
+                src16[r] = r;
+                c16[r] = cplx(1.0, 0.0);
+            }
+            for (size_t i = 0; i < sel.size(); ++i) {
+                if (role[i] != which) continue;
+                any = true;
+                const TileOp& op = ops[sel[i]];
+                int rb[3];
+                for (int j = 0; j < op.k; ++j) rb[j] = rank_in(S, op.bits[j]);
+                int nsrc[CL_REGS];
+                cplx nc[CL_REGS];
+                for (int r = 0; r < CL_REGS; ++r) {
+                    int rr = 0;
+                    for (int j = 0; j < op.k; ++j) rr |= ((r >> rb[j]) & 1) << j;
+                    int x = r;
+                    for (int j = 0; j < op.k; ++j) x = (x & ~(1 << rb[j])) | (((op.src[rr] >> j) & 1) << rb[j]);
+                    nsrc[r] = src16[x];
+                    nc[r] = op.m[rr] * c16[x];
+                }
+                memcpy(src16, nsrc, sizeof nsrc);
+                for (int r = 0; r < CL_REGS; ++r) c16[r] = nc[r];
+            }
+            return any;
+        };
+        uint64_t rperm = CL_PERM_ID, wperm = CL_PERM_ID;
+        ph.rcoef = ph.wcoef = CL_NOCOEF;
+        {
+            int src16[CL_REGS];
+            cplx c16[CL_REGS];
+            if (compose(1, src16, c16)) {  // v[r] = c[r] * slot[src[r]]
+                rperm = 0;
+                bool unit = true;
+                for (int r = 0; r < CL_REGS; ++r) {
+                    rperm |= (uint64_t)src16[r] << (4 * r);
+                    unit &= (c16[r] == cplx(1.0, 0.0));
+                }
+                if (!unit) {
+                    ph.rcoef = (uint32_t)data.size();
+                    for (int r = 0; r < CL_REGS; ++r) data.push_back(make_double2(c16[r].real(), c16[r].imag()));
+                }
+            }
+            if (compose(2, src16, c16)) {  // slot[r] = c[r] * v[src[r]]  ->  register q goes to slot dst[q]
+                wperm = 0;
+                bool unit = true;
+                cplx cq[CL_REGS];
+                for (int r = 0; r < CL_REGS; ++r) {
+                    wperm |= (uint64_t)r << (4 * src16[r]);
+                    cq[src16[r]] = c16[r];
+                    unit &= (c16[r] == cplx(1.0, 0.0));
+                }
+                if (!unit) {
+                    ph.wcoef = (uint32_t)data.size();
+                    for (int q = 0; q < CL_REGS; ++q) data.push_back(make_double2(cq[q].real(), cq[q].imag()));
+                }
+            }
+        }
+        ph.rperm_lo = (uint32_t)rperm;
+        ph.rperm_hi = (uint32_t)(rperm >> 32);
+        ph.wperm_lo = (uint32_t)wperm;
+        ph.wperm_hi = (uint32_t)(wperm >> 32);
+        std::vector<int> mid;
+        for (size_t i = 0; i < sel.size(); ++i)
+            if (!role[i]) mid.push_back(sel[i]);
         ph.sub_first = (uint16_t)subs.size();
-        ph.nsub = (uint8_t)sel.size();
-        if (sel.size() > 255 || subs.size() + sel.size() > 65535)
+        ph.nsub = (uint8_t)mid.size();
+        if (mid.size() > 255 || subs.size() + mid.size() > 65535)
             QSV_FAIL(QSV_ERR_UNSUPPORTED, "internal: too many ops in one pass");
-        for (int id : sel) {
+        for (int id : mid) {
             const TileOp& op = ops[id];
             ClSub sb;
             memset(&sb, 0, sizeof sb);
@@ -1151,7 +1299,8 @@ static int build_cluster_pass(qsv_state* s, const std::vector<HGate>& gates, con
                     uint32_t roff = 0;
                     for (int j = 0; j < CL_R; ++j) roff |= (uint32_t)((r >> j) & 1) << ph.rpos[j];
                     uint32_t part = 0;
-                    for (int j = 0; j < op.k; ++j) part |= ((roff >> op.bits[j]) & 1u) << j;
+                    for (int j = 0; j < op.k; ++j)
+                        if (op.bits[j] < 64) part |= ((roff >> op.bits[j]) & 1u) << j;
                     sb.regpart[r] = (uint16_t)part;
                 }
                 for (const cplx& v : op.m) data.push_back(make_double2(v.real(), v.imag()));
@@ -1206,21 +1355,21 @@ static int build_cluster_pass(qsv_state* s, const std::vector<HGate>& gates, con
     return QSV_OK;
 }
 
-template <int NT>
+template <int NT, int SETS>
 static int launch_cluster_nt(qsv_state* s, const ClPass& P, uint64_t ntiles) {
     const size_t smem = (size_t)16 << P.T;
-    QSV_CUDA(cudaFuncSetAttribute(k_cluster_pass<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_cluster_pass<NT><<<(unsigned)ntiles, NT, smem, s->stream>>>(s->amp, P);
+    QSV_CUDA(cudaFuncSetAttribute(k_cluster_pass<NT, SETS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_cluster_pass<NT, SETS><<<(unsigned)ntiles, NT, smem, s->stream>>>(s->amp, P);
     return QSV_OK;
 }
 
 static int launch_cluster_pass(qsv_state* s, const ClPass& P, uint64_t ntiles) {
     if (ntiles > 0x7fffffffull) QSV_FAIL(QSV_ERR_UNSUPPORTED, "too many tiles for one launch");
     switch (P.T) {
-        case 10: QSV_TRY(launch_cluster_nt<64>(s, P, ntiles)); break;
-        case 11: QSV_TRY(launch_cluster_nt<128>(s, P, ntiles)); break;
-        case 12: QSV_TRY(launch_cluster_nt<256>(s, P, ntiles)); break;
-        case 13: QSV_TRY(launch_cluster_nt<512>(s, P, ntiles)); break;
+        case 10: QSV_TRY((launch_cluster_nt<64, 1>(s, P, ntiles))); break;
+        case 11: QSV_TRY((launch_cluster_nt<128, 1>(s, P, ntiles))); break;
+        case 12: QSV_TRY((launch_cluster_nt<128, 2>(s, P, ntiles))); break;
+        case 13: QSV_TRY((launch_cluster_nt<128, 4>(s, P, ntiles))); break;
         default: QSV_FAIL(QSV_ERR_UNSUPPORTED, "internal: cluster pass with %d tile bits", P.T);
     }
     QSV_CUDA(cudaGetLastError());
@@ -1279,7 +1428,8 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
             std::vector<HGate> seg(gates.begin() + start, gates.begin() + end);
             std::vector<PassPlan> passes;
             const int T = s->tile_bits;
-            plan_passes(seg, s->n_local, T, s->low_bits, no_fusion, passes);
+            const bool cluster = s->use_cluster && std::min(T, s->n_local) >= 10;
+            plan_passes(seg, s->n_local, T, s->low_bits, no_fusion, cluster, passes);
             std::vector<PassParams> params(passes.size());
             std::vector<ClPass> cparams(passes.size());
             std::vector<size_t> ops_off(passes.size()), data_off(passes.size()), subs_off(passes.size());
@@ -1288,7 +1438,7 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
             for (size_t i = 0; i < passes.size(); ++i) {
                 if (s->use_direct && passes[i].gate_ids.size() == 1 && direct_capable(seg[passes[i].gate_ids[0]])) {
                     kind[i] = 2;
-                } else if (s->use_cluster && std::min(T, s->n_local) >= 10) {
+                } else if (cluster) {
                     kind[i] = 1;
                     QSV_TRY(build_cluster_pass(s, seg, passes[i], T, stage, cparams[i], ops_off[i], subs_off[i],
                                                data_off[i]));
