@@ -166,6 +166,17 @@ int qsv_dist_unique_id(void* out128);
 int qsv_create_dist(qsv_state** out, int n_qubits, int device, int rank, int world,
                     const void* unique_id128);
 int qsv_dist_info(const qsv_state* s, int* rank, int* world, int* n_local);
+/* Host-only view of the sharded gate scheduler (no device work; used by the CPU tests that
+ * replay the schedule on NumPy slabs over gloo).  Gate i acts on logical qubits
+ * qargs[i*QSV_MAX_GATE_QUBITS ...] (ks[i] of them); need[i] has bit j set when slot j must be
+ * local (qsv_dist_need_mask).  perm_in[q] = physical bit of logical qubit q (NULL: identity).
+ * The schedule is written as int32 words:  0, count, gate indices...  (apply in this order) or
+ * 1, k, (in_qubit, out_qubit) x k  (swap: logical in_qubit becomes local, out_qubit global). */
+int qsv_dist_plan(int n_qubits, int world, const int* perm_in, uint64_t n_gates, const int32_t* ks,
+                  const int32_t* qargs, const uint32_t* need, int min_lpos, int32_t* out_words,
+                  uint64_t cap_words, uint64_t* n_words, int* perm_out);
+/* slots of a gate that are not block diagonal (must be local before the gate can be applied) */
+int qsv_dist_need_mask(const qsv_gate* gate, uint32_t* out);
 
 #ifdef __cplusplus
 }

@@ -450,3 +450,47 @@ def tree_choice_indices(p: np.ndarray, uniforms: np.ndarray) -> np.ndarray:
         x = np.where(j > 0, x + prev, x)
         blk = base + j
     return blk
+
+
+def tree_choice_indices_sharded(p: np.ndarray, uniforms: np.ndarray, world: int) -> np.ndarray:
+    """The engine's tree for a state split over ``world`` ranks (csrc/qsv_sample.cu): each rank
+    builds the tree above over its own slab; the rank totals t_r are chained sequentially,
+    chain[r+1] = fl(chain[r] + t_r); a uniform belongs to the first rank with
+    fl(chain[r+1] / total) > u (clamped to the last rank) and descends that rank's tree with
+    X = chain[r]."""
+    p = np.asarray(p, dtype=np.float64)
+    u = np.asarray(uniforms, dtype=np.float64)
+    slabs = p.reshape(world, -1)
+    levels = [tree_levels(s) for s in slabs]
+    tot = [lv[-1][0][lv[-1][1] - 1] for lv in levels]
+    chain = [0.0]
+    for r in range(world):
+        chain.append(tot[r] if r == 0 else chain[-1] + tot[r])
+    total = chain[-1]
+    owner = np.full(u.shape, world - 1, dtype=np.int64)
+    for r in range(world - 2, -1, -1):
+        owner = np.where((chain[r + 1] / total) > u, r, owner)
+    out = np.zeros(u.shape, dtype=np.int64)
+    for r in range(world):
+        sel = np.nonzero(owner == r)[0]
+        if sel.size == 0:
+            continue
+        x = np.full(sel.shape, chain[r], dtype=np.float64)
+        blk = np.zeros(sel.shape, dtype=np.int64)
+        uu = u[sel]
+        for w, n_valid in reversed(levels[r]):
+            base = blk * BLK
+            last = np.minimum(BLK, n_valid - base) - 1
+            lo = np.zeros(sel.shape, dtype=np.int64)
+            hi = last.copy()
+            while np.any(lo < hi):
+                mid = (lo + hi) >> 1
+                hit = ((x + w[base + mid]) / total) > uu
+                hi = np.where(hit, mid, hi)
+                lo = np.where(hit, lo, np.minimum(mid + 1, hi))
+            j = lo
+            prev = w[base + np.maximum(j - 1, 0)]
+            x = np.where(j > 0, x + prev, x)
+            blk = base + j
+        out[sel] = blk + r * slabs.shape[1]
+    return out

@@ -86,6 +86,8 @@ PROTOTYPES = {
     "qsv_dist_unique_id": (_i, [_vp]),
     "qsv_create_dist": (_i, [_P(_vp), _i, _i, _i, _i, _vp]),
     "qsv_dist_info": (_i, [_vp, _P(_i), _P(_i), _P(_i)]),
+    "qsv_dist_plan": (_i, [_i, _i, _P(_i), _u64, _vp, _vp, _vp, _i, _vp, _u64, _P(_u64), _P(_i)]),
+    "qsv_dist_need_mask": (_i, [_P(QsvGate), _P(C.c_uint32)]),
 }
 
 _lib = None

@@ -1,42 +1,246 @@
-// Sharded states: one process per GPU, NCCL over NVLink (loaded with dlopen so the
-// single-GPU path has no NCCL dependency).  Placeholder until the exchange kernels land.
+// Sharded states: one process per GPU, 2^g ranks, rank r holds the slab whose top g index bits
+// equal r.  Gates on local qubits need no communication; gates that are block
+// diagonal in a global qubit (diagonal gates, controls) are applied per rank with the block its
+// rank bits select; everything else first makes the qubit local with a GLOBAL<->LOCAL QUBIT SWAP.
+//
+// The swap is an all-to-all between the 2^k ranks that differ in the k swapped global bits.
+// Two transports, same semantics:
+//   * P2P (default when CUDA IPC peer mapping works): ONE kernel per rank exchanges, in place and
+//     without scratch, its sub-slabs with the peers' over NVLink (peer loads + peer stores; each
+//     pair of ranks splits a sub-slab in halves so every element pair is moved by exactly one
+//     thread).  Cross-rank ordering comes from 1-element NCCL all-reduces on the same stream.
+//   * NCCL: pack kernel -> grouped ncclSend/ncclRecv through a bounded scratch ring -> unpack.
+// NCCL (dlopen'ed, so a single-GPU process never needs it) also carries the expectation-value
+// all-reduce and the sampling all-gather.
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+
 #include "qsv_common.cuh"
 
-#include <complex>
+#define MAX_RANKS 16
+#define MAX_G 4
 
+struct NcclApi {
+    void* lib;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*);
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int);
+    ncclResult_t (*CommDestroy)(ncclComm_t);
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t);
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t);
+    ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+    ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+    ncclResult_t (*GroupStart)();
+    ncclResult_t (*GroupEnd)();
+    const char* (*GetErrorString)(ncclResult_t);
+};
+static NcclApi g_nccl;
 
-void qsv_dist_free(qsv_state* s) { (void)s; }
-
-int qsv_dist_canonicalize(qsv_state* s) {
-    for (int q = 0; q < s->n; ++q)
-        if (s->perm[q] != q) QSV_FAIL(QSV_ERR_UNSUPPORTED, "sharded layout restore not implemented");
+static int nccl_load() {
+    if (g_nccl.lib) return QSV_OK;
+    const char* names[] = {getenv("QSV_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+    void* lib = nullptr;
+    for (const char* nm : names) {
+        if (!nm || !*nm) continue;
+        lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+        if (lib) break;
+    }
+    if (!lib) QSV_FAIL(QSV_ERR_NCCL, "cannot dlopen libnccl.so.2: %s", dlerror());
+#define LOAD(field, sym)                                                        \
+    do {                                                                        \
+        *(void**)(&g_nccl.field) = dlsym(lib, sym);                             \
+        if (!g_nccl.field) QSV_FAIL(QSV_ERR_NCCL, "libnccl lacks symbol %s", sym); \
+    } while (0)
+    LOAD(GetUniqueId, "ncclGetUniqueId");
+    LOAD(CommInitRank, "ncclCommInitRank");
+    LOAD(CommDestroy, "ncclCommDestroy");
+    LOAD(AllReduce, "ncclAllReduce");
+    LOAD(AllGather, "ncclAllGather");
+    LOAD(Send, "ncclSend");
+    LOAD(Recv, "ncclRecv");
+    LOAD(GroupStart, "ncclGroupStart");
+    LOAD(GroupEnd, "ncclGroupEnd");
+    LOAD(GetErrorString, "ncclGetErrorString");
+#undef LOAD
+    g_nccl.lib = lib;
     return QSV_OK;
 }
 
-int qsv_dist_apply(qsv_state* s, std::vector<HGate>& gates, int flags) {
-    (void)s; (void)gates; (void)flags;
-    QSV_FAIL(QSV_ERR_UNSUPPORTED, "sharded gate application not implemented");
+#define QSV_NCCL(expr)                                                                          \
+    do {                                                                                        \
+        ncclResult_t r__ = (expr);                                                              \
+        if (r__ != ncclSuccess) {                                                               \
+            qsv_set_error("NCCL error at %s:%d: %s", __FILE__, __LINE__, g_nccl.GetErrorString(r__)); \
+            return QSV_ERR_NCCL;                                                                \
+        }                                                                                       \
+    } while (0)
+
+struct qsv_dist {
+    ncclComm_t comm;
+    int g;                         // log2(world)
+    int p2p;                       // peer slabs mapped through CUDA IPC
+    int use_p2p;                   // transport choice (option "dist_p2p")
+    double2* peer_amp[MAX_RANKS];  // peer_amp[rank] = own slab
+    void* ipc_base[MAX_RANKS];     // pointers returned by cudaIpcOpenMemHandle (to close)
+    double* d_tok;                 // small device buffer: barrier token, gathers
+    void* xbuf;                    // NCCL transport scratch
+    size_t xbuf_bytes;
+    int min_lpos;                  // lowest local bit position the planner may evict
+};
+
+void qsv_dist_free(qsv_state* s) {
+    qsv_dist* d = s->dist;
+    if (!d) return;
+    cudaStreamSynchronize(s->stream);
+    for (int r = 0; r < s->world; ++r)
+        if (d->ipc_base[r]) cudaIpcCloseMemHandle(d->ipc_base[r]);
+    if (d->d_tok) cudaFree(d->d_tok);
+    if (d->xbuf) cudaFree(d->xbuf);
+    if (d->comm) g_nccl.CommDestroy(d->comm);
+    delete d;
+    s->dist = nullptr;
+}
+
+// stream-ordered barrier across ranks: nobody's later work starts before everybody's earlier
+// work on the handle's stream has finished
+static int dist_barrier(qsv_state* s) {
+    qsv_dist* d = s->dist;
+    QSV_NCCL(g_nccl.AllReduce(d->d_tok, d->d_tok, 1, ncclDouble, ncclSum, d->comm, s->stream));
+    return QSV_OK;
 }
 
 int qsv_dist_allreduce_sum(qsv_state* s, double* dev_buf, size_t count) {
-    (void)s; (void)dev_buf; (void)count;
-    QSV_FAIL(QSV_ERR_UNSUPPORTED, "sharded reductions not implemented");
+    if (!s->dist) QSV_FAIL(QSV_ERR_INVALID, "state is not sharded");
+    QSV_NCCL(g_nccl.AllReduce(dev_buf, dev_buf, count, ncclDouble, ncclSum, s->dist->comm, s->stream));
+    return QSV_OK;
 }
 
-int qsv_dist_localize_xmask(qsv_state* s, uint64_t phys_x_mask) {
-    (void)s; (void)phys_x_mask;
-    QSV_FAIL(QSV_ERR_UNSUPPORTED, "sharded expval with global X bits not implemented");
+int qsv_dist_allreduce_sum_u64(qsv_state* s, uint64_t* dev_buf, size_t count) {
+    if (!s->dist) QSV_FAIL(QSV_ERR_INVALID, "state is not sharded");
+    QSV_NCCL(g_nccl.AllReduce(dev_buf, dev_buf, count, ncclUint64, ncclSum, s->dist->comm, s->stream));
+    return QSV_OK;
+}
+
+// out[world * count] <- every rank's in[count]
+int qsv_dist_allgather(qsv_state* s, const double* dev_in, double* dev_out, size_t count) {
+    if (!s->dist) QSV_FAIL(QSV_ERR_INVALID, "state is not sharded");
+    QSV_NCCL(g_nccl.AllGather(dev_in, dev_out, count, ncclDouble, s->dist->comm, s->stream));
+    return QSV_OK;
 }
 
 extern "C" int qsv_dist_unique_id(void* out128) {
-    (void)out128;
-    QSV_FAIL(QSV_ERR_UNSUPPORTED, "sharded states not implemented");
+    if (!out128) QSV_FAIL(QSV_ERR_INVALID, "qsv_dist_unique_id: out is NULL");
+    QSV_TRY(nccl_load());
+    ncclUniqueId id;
+    QSV_NCCL(g_nccl.GetUniqueId(&id));
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId size");
+    memcpy(out128, &id, 128);
+    return QSV_OK;
 }
 
 extern "C" int qsv_create_dist(qsv_state** out, int n_qubits, int device, int rank, int world,
                                const void* unique_id128) {
-    (void)out; (void)n_qubits; (void)device; (void)rank; (void)world; (void)unique_id128;
-    QSV_FAIL(QSV_ERR_UNSUPPORTED, "sharded states not implemented");
+    if (!out || !unique_id128) QSV_FAIL(QSV_ERR_INVALID, "qsv_create_dist: NULL argument");
+    *out = nullptr;
+    int g = 0;
+    while ((1 << g) < world) ++g;
+    if (world < 2 || (1 << g) != world || world > MAX_RANKS)
+        QSV_FAIL(QSV_ERR_INVALID, "qsv_create_dist: world = %d must be a power of two in [2, %d]", world, MAX_RANKS);
+    if (rank < 0 || rank >= world) QSV_FAIL(QSV_ERR_INVALID, "qsv_create_dist: rank %d outside [0, %d)", rank, world);
+    if (n_qubits - g < g + 1)
+        QSV_FAIL(QSV_ERR_INVALID, "qsv_create_dist: %d qubits are too few to shard over %d ranks", n_qubits, world);
+    QSV_TRY(nccl_load());
+    qsv_state* s = nullptr;
+    QSV_TRY(qsv_state_alloc(&s, n_qubits, n_qubits - g, device, nullptr));
+    s->rank = rank;
+    s->world = world;
+    qsv_dist* d = new qsv_dist();
+    memset(d, 0, sizeof *d);
+    d->g = g;
+    s->dist = d;
+    d->min_lpos = s->n_local >= 16 ? 5 : 0;
+    ncclUniqueId id;
+    memcpy(&id, unique_id128, 128);
+    int rc = QSV_OK;
+    do {
+        ncclResult_t r = g_nccl.CommInitRank(&d->comm, world, id, rank);
+        if (r != ncclSuccess) {
+            qsv_set_error("ncclCommInitRank failed: %s", g_nccl.GetErrorString(r));
+            rc = QSV_ERR_NCCL;
+            break;
+        }
+        // token + gather area: [0] token, [8 ...] handles / totals
+        if (cudaMalloc((void**)&d->d_tok, 4096) != cudaSuccess) {
+            qsv_set_error("cudaMalloc of the sharding token buffer failed");
+            rc = QSV_ERR_NOMEM;
+            break;
+        }
+        cudaMemsetAsync(d->d_tok, 0, 4096, s->stream);
+        // exchange CUDA IPC handles of the slabs through NCCL itself (no other channel needed)
+        cudaIpcMemHandle_t mine;
+        static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle size");
+        d->peer_amp[rank] = s->amp;
+        d->p2p = 0;
+        const char* env = getenv("QSV_DIST_P2P");
+        const int want_p2p = env && *env ? atoi(env) : 1;
+        int ok = want_p2p && cudaIpcGetMemHandle(&mine, s->amp) == cudaSuccess;
+        if (!ok) {
+            cudaGetLastError();
+            memset(&mine, 0, sizeof mine);
+        }
+        char* d_h = (char*)d->d_tok + 64;            // world * 64 bytes of handles, then flags
+        char* d_mine = d_h + MAX_RANKS * 64;
+        cudaMemcpyAsync(d_mine, &mine, 64, cudaMemcpyHostToDevice, s->stream);
+        r = g_nccl.AllGather(d_mine, d_h, 64, ncclChar, d->comm, s->stream);
+        if (r != ncclSuccess) {
+            qsv_set_error("ncclAllGather of IPC handles failed: %s", g_nccl.GetErrorString(r));
+            rc = QSV_ERR_NCCL;
+            break;
+        }
+        cudaIpcMemHandle_t all[MAX_RANKS];
+        cudaMemcpyAsync(all, d_h, 64 * world, cudaMemcpyDeviceToHost, s->stream);
+        if (cudaStreamSynchronize(s->stream) != cudaSuccess) {
+            qsv_set_error("sharded setup: stream failed: %s", cudaGetErrorString(cudaGetLastError()));
+            rc = QSV_ERR_CUDA;
+            break;
+        }
+        if (ok) {
+            for (int p = 0; p < world && ok; ++p) {
+                if (p == rank) continue;
+                void* base = nullptr;
+                if (cudaIpcOpenMemHandle(&base, all[p], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                    cudaGetLastError();
+                    ok = 0;
+                    break;
+                }
+                d->ipc_base[p] = base;
+                d->peer_amp[p] = (double2*)base;
+            }
+        }
+        // every rank must take the same transport: min over ranks of `ok`
+        double flag = ok ? 1.0 : 0.0, *d_flag = d->d_tok + 1;
+        cudaMemcpyAsync(d_flag, &flag, 8, cudaMemcpyHostToDevice, s->stream);
+        r = g_nccl.AllReduce(d_flag, d_flag, 1, ncclDouble, ncclMin, d->comm, s->stream);
+        if (r != ncclSuccess) {
+            qsv_set_error("ncclAllReduce failed: %s", g_nccl.GetErrorString(r));
+            rc = QSV_ERR_NCCL;
+            break;
+        }
+        cudaMemcpyAsync(&flag, d_flag, 8, cudaMemcpyDeviceToHost, s->stream);
+        cudaStreamSynchronize(s->stream);
+        d->p2p = flag > 0.5;
+        d->use_p2p = d->p2p;
+    } while (0);
+    if (rc != QSV_OK) {
+        std::string msg = qsv_last_error();
+        qsv_destroy(s);
+        qsv_set_error("%s", msg.c_str());
+        return rc;
+    }
+    QSV_TRY(qsv_init_basis(s, 0));
+    *out = s;
+    return QSV_OK;
 }
 
 extern "C" int qsv_dist_info(const qsv_state* s, int* rank, int* world, int* n_local) {
@@ -44,5 +248,525 @@ extern "C" int qsv_dist_info(const qsv_state* s, int* rank, int* world, int* n_l
     if (rank) *rank = s->rank;
     if (world) *world = s->world;
     if (n_local) *n_local = s->n_local;
+    return QSV_OK;
+}
+
+int qsv_dist_set_option(qsv_state* s, const char* name, int64_t value) {
+    if (!s->dist) QSV_FAIL(QSV_ERR_INVALID, "option '%s' needs a sharded state", name);
+    if (!strcmp(name, "dist_p2p")) {
+        if (value && !s->dist->p2p) QSV_FAIL(QSV_ERR_UNSUPPORTED, "peer slabs are not mapped (CUDA IPC unavailable)");
+        s->dist->use_p2p = value != 0;
+        return QSV_OK;
+    }
+    if (!strcmp(name, "dist_min_lpos")) {
+        if (value < 0 || value > s->n_local - s->dist->g - 1) QSV_FAIL(QSV_ERR_INVALID, "dist_min_lpos out of range");
+        s->dist->min_lpos = (int)value;
+        return QSV_OK;
+    }
+    QSV_FAIL(QSV_ERR_INVALID, "qsv_set_option: unknown option '%s'", name);
+}
+
+// ------------------------------------------------------------------ the qubit swap ---------
+// Swap k global bits with k local bits.  Let a = this rank's value on the swapped global bits and
+// j = an amplitude's value on the chosen local bits: amplitude (G = a, L = j) trades places with
+// (G = j, L = a).  Rank a therefore exchanges its sub-slab L = j with peer j's sub-slab L = a,
+// for every j != a; sub-slab L = a stays.
+struct SwapArgs {
+    double2* peer[1 << MAX_G];  // slab of the rank whose swapped global bits read j (peer[a] unused)
+    int k;
+    int lsorted[MAX_G];         // local bit positions, ascending (zero insertion)
+    int lpos[MAX_G];            // local bit paired with swapped global bit i
+    int a;
+    uint64_t rest;              // 2^(n_local - k) amplitudes per sub-slab
+};
+
+__device__ __forceinline__ uint64_t swap_expand(uint64_t idx, const SwapArgs& A) {
+    for (int i = 0; i < A.k; ++i) idx = insert_zero(idx, A.lsorted[i]);
+    return idx;
+}
+
+// P2P transport.  grid = (blocks, 2^k - 1); pair (a, j) splits the sub-slab: the lower rank value
+// moves the first half, the higher one the second half, so no element is touched twice.
+__global__ void __launch_bounds__(256) k_swap_p2p(double2* __restrict__ mine, const __grid_constant__ SwapArgs A) {
+    const int j = (int)blockIdx.y < A.a ? (int)blockIdx.y : (int)blockIdx.y + 1;
+    double2* __restrict__ peer = A.peer[j];
+    uint64_t my_off = 0, peer_off = 0;
+    for (int i = 0; i < A.k; ++i) {
+        my_off |= (uint64_t)((j >> i) & 1) << A.lpos[i];
+        peer_off |= (uint64_t)((A.a >> i) & 1) << A.lpos[i];
+    }
+    const uint64_t half = A.rest >> 1;
+    const uint64_t lo = A.a < j ? 0 : half, hi = lo + half;
+    const uint64_t stride = (uint64_t)gridDim.x * 256;
+    uint64_t idx = lo + blockIdx.x * 256ull + threadIdx.x;
+    // four independent element pairs in flight per thread (peer loads have ~2 us latency)
+    for (; idx + 3 * stride < hi; idx += 4 * stride) {
+        uint64_t b[4];
+        double2 x[4], y[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) b[u] = swap_expand(idx + u * stride, A);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) y[u] = peer[b[u] | peer_off];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) x[u] = mine[b[u] | my_off];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            mine[b[u] | my_off] = y[u];
+            peer[b[u] | peer_off] = x[u];
+        }
+    }
+    for (; idx < hi; idx += stride) {
+        const uint64_t b = swap_expand(idx, A);
+        const double2 y = peer[b | peer_off], x = mine[b | my_off];
+        mine[b | my_off] = y;
+        peer[b | peer_off] = x;
+    }
+}
+
+// NCCL transport: gather sub-slab elements [c0, c0 + cnt) for every peer into a send buffer ...
+__global__ void __launch_bounds__(256) k_swap_pack(const double2* __restrict__ mine, const __grid_constant__ SwapArgs A,
+                                                   uint64_t c0, uint64_t cnt, double2* __restrict__ sendbuf) {
+    const int jj = blockIdx.y, j = jj < A.a ? jj : jj + 1;
+    uint64_t my_off = 0;
+    for (int i = 0; i < A.k; ++i) my_off |= (uint64_t)((j >> i) & 1) << A.lpos[i];
+    const uint64_t stride = (uint64_t)gridDim.x * 256;
+    for (uint64_t i = blockIdx.x * 256ull + threadIdx.x; i < cnt; i += stride)
+        sendbuf[(uint64_t)jj * cnt + i] = mine[swap_expand(c0 + i, A) | my_off];
+}
+// ... and scatter what the peers sent into the same places
+__global__ void __launch_bounds__(256) k_swap_unpack(double2* __restrict__ mine, const __grid_constant__ SwapArgs A,
+                                                     uint64_t c0, uint64_t cnt, const double2* __restrict__ recvbuf) {
+    const int jj = blockIdx.y, j = jj < A.a ? jj : jj + 1;
+    uint64_t my_off = 0;
+    for (int i = 0; i < A.k; ++i) my_off |= (uint64_t)((j >> i) & 1) << A.lpos[i];
+    const uint64_t stride = (uint64_t)gridDim.x * 256;
+    for (uint64_t i = blockIdx.x * 256ull + threadIdx.x; i < cnt; i += stride)
+        mine[swap_expand(c0 + i, A) | my_off] = recvbuf[(uint64_t)jj * cnt + i];
+}
+
+// Exchange physical global bits gpos[i] (>= n_local) with physical local bits lpos[i], i < k.
+static int dist_swap_bits(qsv_state* s, int k, const int* gpos, const int* lpos) {
+    qsv_dist* d = s->dist;
+    if (k < 1 || k > d->g) QSV_FAIL(QSV_ERR_INVALID, "internal: swap of %d bits", k);
+    SwapArgs A;
+    memset(&A, 0, sizeof A);
+    A.k = k;
+    A.rest = 1ull << (s->n_local - k);
+    int peers_rank[1 << MAX_G];
+    for (int i = 0; i < k; ++i) {
+        A.lpos[i] = lpos[i];
+        A.lsorted[i] = lpos[i];
+        A.a |= ((s->rank >> (gpos[i] - s->n_local)) & 1) << i;
+    }
+    std::sort(A.lsorted, A.lsorted + k);
+    for (int j = 0; j < (1 << k); ++j) {
+        int r = s->rank;
+        for (int i = 0; i < k; ++i) {
+            const int bit = gpos[i] - s->n_local;
+            r = (r & ~(1 << bit)) | (((j >> i) & 1) << bit);
+        }
+        peers_rank[j] = r;
+        A.peer[j] = d->peer_amp[r];
+    }
+    const int npeers = (1 << k) - 1;
+    cudaEvent_t e0 = s->ev0;  // not used for timing here; transport time is measured by callers
+    (void)e0;
+    if (d->use_p2p) {
+        QSV_TRY(dist_barrier(s));
+        uint64_t blocks = ((A.rest >> 1) + 256 * 4 - 1) / (256 * 4);
+        const uint64_t cap = (uint64_t)s->num_sms * 8 / npeers + 1;
+        if (blocks > cap) blocks = cap;
+        if (blocks < 1) blocks = 1;
+        k_swap_p2p<<<dim3((unsigned)blocks, npeers), 256, 0, s->stream>>>(s->amp, A);
+        QSV_CUDA(cudaGetLastError());
+        s->ctr.kernel_launches++;
+        QSV_TRY(dist_barrier(s));
+    } else {
+        // scratch: send + recv, npeers * chunk elements each
+        if (!d->xbuf) {
+            size_t free_b = 0, total_b = 0;
+            QSV_CUDA(cudaMemGetInfo(&free_b, &total_b));
+            size_t want = std::min<size_t>((size_t)4 << 30, free_b / 2);
+            want = std::min<size_t>(want, std::max<size_t>((size_t)32 << s->n_local, (size_t)1 << 20));  // <= two slabs
+            want &= ~(size_t)4095;
+            if (want < (1u << 16)) QSV_FAIL(QSV_ERR_NOMEM, "no device memory left for the exchange scratch");
+            QSV_CUDA(cudaMalloc(&d->xbuf, want));
+            d->xbuf_bytes = want;
+        }
+        uint64_t chunk = d->xbuf_bytes / (2ull * npeers * 16);
+        if (chunk > A.rest) chunk = A.rest;
+        double2* sendbuf = (double2*)d->xbuf;
+        double2* recvbuf = sendbuf + (uint64_t)npeers * chunk;
+        for (uint64_t c0 = 0; c0 < A.rest; c0 += chunk) {
+            const uint64_t cnt = std::min<uint64_t>(chunk, A.rest - c0);
+            uint64_t blocks = (cnt + 255) / 256;
+            const uint64_t cap = (uint64_t)s->num_sms * 8 / npeers + 1;
+            if (blocks > cap) blocks = cap;
+            k_swap_pack<<<dim3((unsigned)blocks, npeers), 256, 0, s->stream>>>(s->amp, A, c0, cnt, sendbuf);
+            QSV_CUDA(cudaGetLastError());
+            QSV_NCCL(g_nccl.GroupStart());
+            for (int jj = 0; jj < npeers; ++jj) {
+                const int j = jj < A.a ? jj : jj + 1;
+                QSV_NCCL(g_nccl.Send(sendbuf + (uint64_t)jj * cnt, cnt * 2, ncclDouble, peers_rank[j], d->comm, s->stream));
+                QSV_NCCL(g_nccl.Recv(recvbuf + (uint64_t)jj * cnt, cnt * 2, ncclDouble, peers_rank[j], d->comm, s->stream));
+            }
+            QSV_NCCL(g_nccl.GroupEnd());
+            k_swap_unpack<<<dim3((unsigned)blocks, npeers), 256, 0, s->stream>>>(s->amp, A, c0, cnt, recvbuf);
+            QSV_CUDA(cudaGetLastError());
+            s->ctr.kernel_launches += 2;
+        }
+    }
+    s->ctr.swap_count++;
+    s->ctr.swap_bytes += (uint64_t)npeers * A.rest * 16;
+    // the logical qubits that sat on those physical bits trade places
+    for (int q = 0; q < s->n; ++q) {
+        for (int i = 0; i < k; ++i) {
+            if (s->perm[q] == gpos[i]) { s->perm[q] = lpos[i]; break; }
+            if (s->perm[q] == lpos[i]) { s->perm[q] = gpos[i]; break; }
+        }
+    }
+    return QSV_OK;
+}
+
+// ------------------------------------------------------------------ planner (host only) -----
+// A gate needs qubit slot j LOCAL unless its matrix is block diagonal in that slot (the slot's bit
+// is the same in the row and column index of every non-zero entry): diagonal gates need nothing,
+// a controlled gate needs only its targets.
+static uint32_t need_local_mask(const HGate& g) {
+    if (g.diag) return 0;
+    const int dim = 1 << g.k;
+    uint32_t need = 0;
+    for (int r = 0; r < dim; ++r)
+        for (int c = 0; c < dim; ++c)
+            if (g.m[(size_t)r * dim + c] != cplx(0.0, 0.0)) need |= (uint32_t)(r ^ c);
+    return need;
+}
+
+struct PlanGate {
+    int k;
+    int q[QSV_MAX_GATE_QUBITS];  // logical qubits
+    uint32_t need;               // slots that must be local
+};
+struct PlanStep {
+    int kind;                  // 0 = apply gates, 1 = swap
+    std::vector<int> gates;    // kind 0: gate indices, in application order
+    int k;                     // kind 1
+    int gin[MAX_G], lout[MAX_G];  // kind 1: logical qubits coming in (global now) / going out (local now)
+};
+
+// Greedy schedule: run every gate whose needed qubits are local (gates on other qubits may
+// overtake a waiting gate); when none is left, ONE swap brings in every global qubit that is
+// needed sooner than the local qubit it evicts (Belady: evict the qubits needed farthest ahead).
+// A k-bit swap moves (1 - 2^-k) of the slab, so wide swaps are cheap compared with k single ones.
+static int dist_plan(int n, int n_local, const int* perm_in, const std::vector<PlanGate>& gates, int min_lpos,
+                     std::vector<PlanStep>& steps) {
+    const int g = n - n_local;
+    int perm[64];
+    memcpy(perm, perm_in, sizeof(int) * 64);
+    const size_t G = gates.size();
+    std::vector<char> done(G, 0);
+    size_t first = 0;
+    const uint64_t all = n >= 64 ? ~0ull : ((1ull << n) - 1);
+    while (true) {
+        while (first < G && done[first]) ++first;
+        if (first >= G) break;
+        PlanStep run;
+        run.kind = 0;
+        run.k = 0;
+        uint64_t blocked = 0;
+        for (size_t i = first; i < G; ++i) {
+            if (done[i]) continue;
+            const PlanGate& pg = gates[i];
+            uint64_t qm = 0;
+            bool local = true;
+            for (int j = 0; j < pg.k; ++j) {
+                qm |= 1ull << pg.q[j];
+                if (((pg.need >> j) & 1u) && perm[pg.q[j]] >= n_local) local = false;
+            }
+            if ((qm & blocked) || !local) {
+                blocked |= qm;
+                if ((blocked & all) == all) break;
+                continue;
+            }
+            run.gates.push_back((int)i);
+            done[i] = 1;
+        }
+        if (!run.gates.empty()) steps.push_back(std::move(run));
+        while (first < G && done[first]) ++first;
+        if (first >= G) break;
+        // next time each logical qubit is needed local
+        const size_t INF = (size_t)-1;
+        std::vector<size_t> next_need(n, INF);
+        for (size_t i = G; i-- > first;) {
+            if (done[i]) continue;
+            for (int j = 0; j < gates[i].k; ++j)
+                if ((gates[i].need >> j) & 1u) next_need[gates[i].q[j]] = i;
+        }
+        std::vector<int> incoming, victims;
+        for (int q = 0; q < n; ++q)
+            if (perm[q] >= n_local && next_need[q] != INF) incoming.push_back(q);
+        std::sort(incoming.begin(), incoming.end(), [&](int a, int b) { return next_need[a] < next_need[b]; });
+        for (int q = 0; q < n; ++q)
+            if (perm[q] < n_local && perm[q] >= min_lpos) victims.push_back(q);
+        std::sort(victims.begin(), victims.end(), [&](int a, int b) {
+            if (next_need[a] != next_need[b]) return next_need[a] > next_need[b];
+            return perm[a] > perm[b];  // ties: evict high positions (longer contiguous runs)
+        });
+        PlanStep sw;
+        sw.kind = 1;
+        sw.k = 0;
+        for (size_t i = 0; i < incoming.size() && i < victims.size() && sw.k < g; ++i) {
+            if (i > 0 && next_need[victims[i]] <= next_need[incoming[i]]) break;
+            sw.gin[sw.k] = incoming[i];
+            sw.lout[sw.k] = victims[i];
+            ++sw.k;
+        }
+        if (sw.k == 0 || next_need[sw.lout[0]] <= next_need[sw.gin[0]]) {
+            qsv_set_error("sharded schedule: gate %zu needs more local qubits than a slab holds", first);
+            return QSV_ERR_UNSUPPORTED;
+        }
+        for (int i = 0; i < sw.k; ++i) std::swap(perm[sw.gin[i]], perm[sw.lout[i]]);
+        steps.push_back(sw);
+    }
+    return QSV_OK;
+}
+
+// Restrict a gate to this rank: slots on global bits are fixed to the rank's bit values.
+static void restrict_to_rank(const HGate& g, const int* phys, int n_local, int rank, HGate& out, cplx& scalar,
+                             bool& is_scalar) {
+    int keep[QSV_MAX_GATE_QUBITS], nk = 0;
+    int fixed = 0;
+    for (int j = 0; j < g.k; ++j) {
+        if (phys[j] >= n_local) fixed |= ((rank >> (phys[j] - n_local)) & 1) << j;
+        else keep[nk++] = j;
+    }
+    auto expand = [&](int sub) {
+        int full = fixed;
+        for (int t = 0; t < nk; ++t) full |= ((sub >> t) & 1) << keep[t];
+        return full;
+    };
+    const int dim = 1 << g.k, sdim = 1 << nk;
+    is_scalar = nk == 0;
+    if (is_scalar) {
+        scalar = g.diag ? g.m[fixed] : g.m[(size_t)fixed * dim + fixed];
+        return;
+    }
+    out.k = nk;
+    memset(out.q, 0, sizeof out.q);
+    for (int t = 0; t < nk; ++t) out.q[t] = phys[keep[t]];
+    out.diag = g.diag;
+    if (g.diag) {
+        out.m.resize(sdim);
+        for (int i = 0; i < sdim; ++i) out.m[i] = g.m[expand(i)];
+    } else {
+        out.m.resize((size_t)sdim * sdim);
+        for (int r = 0; r < sdim; ++r)
+            for (int c = 0; c < sdim; ++c) out.m[(size_t)r * sdim + c] = g.m[(size_t)expand(r) * dim + expand(c)];
+    }
+}
+
+static int dist_do_swap(qsv_state* s, const PlanStep& st) {
+    int gpos[MAX_G], lpos[MAX_G];
+    for (int i = 0; i < st.k; ++i) {
+        gpos[i] = s->perm[st.gin[i]];
+        lpos[i] = s->perm[st.lout[i]];
+    }
+    return dist_swap_bits(s, st.k, gpos, lpos);
+}
+
+// gates carry LOGICAL qubits in q[]
+int qsv_dist_apply(qsv_state* s, std::vector<HGate>& gates, int flags) {
+    qsv_dist* d = s->dist;
+    if (!d) QSV_FAIL(QSV_ERR_INVALID, "state is not sharded");
+    std::vector<PlanGate> pg(gates.size());
+    for (size_t i = 0; i < gates.size(); ++i) {
+        pg[i].k = gates[i].k;
+        memcpy(pg[i].q, gates[i].q, sizeof pg[i].q);
+        pg[i].need = need_local_mask(gates[i]);
+    }
+    std::vector<PlanStep> steps;
+    QSV_TRY(dist_plan(s->n, s->n_local, s->perm, pg, d->min_lpos, steps));
+    cplx scalar(1.0, 0.0);
+    for (const PlanStep& st : steps) {
+        if (st.kind == 1) {
+            QSV_TRY(dist_do_swap(s, st));
+            continue;
+        }
+        std::vector<HGate> local;
+        local.reserve(st.gates.size());
+        for (int id : st.gates) {
+            const HGate& g = gates[id];
+            int phys[QSV_MAX_GATE_QUBITS];
+            bool any_global = false;
+            for (int j = 0; j < g.k; ++j) {
+                phys[j] = s->perm[g.q[j]];
+                any_global |= phys[j] >= s->n_local;
+            }
+            if (!any_global) {
+                HGate h = g;
+                for (int j = 0; j < g.k; ++j) h.q[j] = phys[j];
+                local.push_back(std::move(h));
+                continue;
+            }
+            HGate h;
+            cplx sc;
+            bool is_scalar;
+            restrict_to_rank(g, phys, s->n_local, s->rank, h, sc, is_scalar);
+            if (is_scalar) {
+                scalar *= sc;
+                continue;
+            }
+            // the block this rank applies is often the identity (control bit 0 on this rank)
+            bool ident = true;
+            const int hd = 1 << h.k;
+            for (int r = 0; r < hd && ident; ++r) {
+                if (h.diag) ident = h.m[r] == cplx(1.0, 0.0);
+                else
+                    for (int c = 0; c < hd && ident; ++c)
+                        ident = h.m[(size_t)r * hd + c] == (r == c ? cplx(1.0, 0.0) : cplx(0.0, 0.0));
+            }
+            if (!ident) local.push_back(std::move(h));
+        }
+        if (scalar != cplx(1.0, 0.0) && !local.empty()) {
+            for (cplx& v : local[0].m) v *= scalar;
+            scalar = cplx(1.0, 0.0);
+        }
+        if (!local.empty()) QSV_TRY(qsv_apply_hgates(s, local, flags));
+    }
+    if (scalar != cplx(1.0, 0.0)) QSV_TRY(qsv_scale(s, scalar.real(), scalar.imag()));
+    return QSV_OK;
+}
+
+int qsv_dist_min_lpos(const qsv_state* s) { return s->dist ? s->dist->min_lpos : 0; }
+
+// Bring the listed logical qubits (bit mask) to local positions, evicting qubits outside `keep`.
+int qsv_dist_localize(qsv_state* s, uint64_t want_local, uint64_t keep) {
+    qsv_dist* d = s->dist;
+    PlanStep sw;
+    sw.kind = 1;
+    sw.k = 0;
+    std::vector<int> victims;
+    for (int q = s->n - 1; q >= 0; --q)
+        if (s->perm[q] < s->n_local && s->perm[q] >= d->min_lpos && !((keep >> q) & 1ull)) victims.push_back(q);
+    std::sort(victims.begin(), victims.end(), [&](int a, int b) { return s->perm[a] > s->perm[b]; });
+    size_t vi = 0;
+    for (int q = 0; q < s->n; ++q) {
+        if (!((want_local >> q) & 1ull) || s->perm[q] < s->n_local) continue;
+        if (vi >= victims.size()) QSV_FAIL(QSV_ERR_UNSUPPORTED, "sharded state: no local qubit left to evict");
+        sw.gin[sw.k] = q;
+        sw.lout[sw.k] = victims[vi++];
+        ++sw.k;
+    }
+    if (sw.k == 0) return QSV_OK;
+    return dist_do_swap(s, sw);
+}
+
+// Restore the identity layout (logical qubit q on physical bit q): global<->local exchanges for
+// the global positions, then SWAP gates inside the slab.
+int qsv_dist_canonicalize(qsv_state* s) {
+    if (!s->dist) return QSV_OK;
+    const int n = s->n, nl = s->n_local;
+    auto at = [&](int pos) {
+        for (int q = 0; q < n; ++q)
+            if (s->perm[q] == pos) return q;
+        return -1;
+    };
+    for (int p = nl; p < n; ++p) {
+        if (s->perm[p] == p) continue;
+        if (s->perm[p] >= nl) {
+            // logical p sits on another global bit: park it on a local bit first
+            int lp = nl - 1;
+            int gp = s->perm[p];
+            QSV_TRY(dist_swap_bits(s, 1, &gp, &lp));
+        }
+        int gp = p, lp = s->perm[p];
+        QSV_TRY(dist_swap_bits(s, 1, &gp, &lp));
+    }
+    // local part: a sequence of physical SWAP gates
+    std::vector<HGate> swaps;
+    for (int pos = 0; pos < nl; ++pos) {
+        const int q = at(pos);
+        if (q == pos) continue;
+        const int other = s->perm[pos];  // where logical `pos` sits now
+        HGate h;
+        h.k = 2;
+        memset(h.q, 0, sizeof h.q);
+        h.q[0] = pos;
+        h.q[1] = other;
+        h.diag = false;
+        h.m.assign(16, cplx(0.0, 0.0));
+        h.m[0] = h.m[6] = h.m[9] = h.m[15] = cplx(1.0, 0.0);
+        swaps.push_back(h);
+        s->perm[q] = other;
+        s->perm[pos] = pos;
+    }
+    if (!swaps.empty()) QSV_TRY(qsv_apply_hgates(s, swaps, 0));
+    return QSV_OK;
+}
+
+// ---- host-only view of the scheduler for tests (no device work) ---------------------------
+// need[i]: bit j set = slot j of gate i must be local.  Steps are written as int32 words:
+//   0, count, gate indices...      apply these gates (in this order)
+//   1, k, (in_qubit, out_qubit) * k   swap: logical in_qubit becomes local, out_qubit global
+extern "C" int qsv_dist_plan(int n_qubits, int world, const int* perm_in, uint64_t n_gates, const int32_t* ks,
+                             const int32_t* qargs /* n_gates x QSV_MAX_GATE_QUBITS */, const uint32_t* need,
+                             int min_lpos, int32_t* out_words, uint64_t cap_words, uint64_t* n_words,
+                             int* perm_out) {
+    if (!ks || !qargs || !need || !n_words) QSV_FAIL(QSV_ERR_INVALID, "qsv_dist_plan: NULL argument");
+    int g = 0;
+    while ((1 << g) < world) ++g;
+    if ((1 << g) != world || n_qubits - g < 1) QSV_FAIL(QSV_ERR_INVALID, "qsv_dist_plan: bad world / qubit count");
+    int perm[64];
+    for (int q = 0; q < 64; ++q) perm[q] = perm_in && q < n_qubits ? perm_in[q] : q;
+    std::vector<PlanGate> pg(n_gates);
+    for (uint64_t i = 0; i < n_gates; ++i) {
+        pg[i].k = ks[i];
+        if (ks[i] < 0 || ks[i] > QSV_MAX_GATE_QUBITS) QSV_FAIL(QSV_ERR_INVALID, "qsv_dist_plan: bad k");
+        for (int j = 0; j < QSV_MAX_GATE_QUBITS; ++j) pg[i].q[j] = qargs[i * QSV_MAX_GATE_QUBITS + j];
+        pg[i].need = need[i];
+    }
+    std::vector<PlanStep> steps;
+    QSV_TRY(dist_plan(n_qubits, n_qubits - g, perm, pg, min_lpos, steps));
+    uint64_t w = 0;
+    auto put = [&](int32_t v) {
+        if (out_words && w < cap_words) out_words[w] = v;
+        ++w;
+    };
+    for (const PlanStep& st : steps) {
+        put(st.kind);
+        if (st.kind == 0) {
+            put((int32_t)st.gates.size());
+            for (int id : st.gates) put(id);
+        } else {
+            put(st.k);
+            for (int i = 0; i < st.k; ++i) {
+                put(st.gin[i]);
+                put(st.lout[i]);
+                std::swap(perm[st.gin[i]], perm[st.lout[i]]);
+            }
+        }
+    }
+    *n_words = w;
+    if (perm_out)
+        for (int q = 0; q < n_qubits; ++q) perm_out[q] = perm[q];
+    if (out_words && w > cap_words) QSV_FAIL(QSV_ERR_INVALID, "qsv_dist_plan: output buffer too small");
+    return QSV_OK;
+}
+
+// need-local slot mask of one gate (same rule the engine uses), for the tests above
+extern "C" int qsv_dist_need_mask(const qsv_gate* gate, uint32_t* out) {
+    if (!gate || !out || !gate->data) QSV_FAIL(QSV_ERR_INVALID, "qsv_dist_need_mask: NULL argument");
+    if (gate->kind == QSV_GATE_DIAGONAL || gate->kind == QSV_GATE_PHASE) {
+        *out = 0;
+        return QSV_OK;
+    }
+    if (gate->k < 0 || gate->k > QSV_MAX_GATE_QUBITS) QSV_FAIL(QSV_ERR_INVALID, "qsv_dist_need_mask: bad k");
+    HGate h;
+    h.k = gate->k;
+    h.diag = false;
+    const size_t dim = (size_t)1 << gate->k;
+    const cplx* src = reinterpret_cast<const cplx*>(gate->data);
+    h.m.assign(src, src + dim * dim);
+    *out = need_local_mask(h);
     return QSV_OK;
 }

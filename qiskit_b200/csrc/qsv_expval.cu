@@ -225,7 +225,8 @@ static int grid_for(const qsv_state* s, uint64_t items) {
 }
 
 int qsv_dist_allreduce_sum(qsv_state* s, double* dev_buf, size_t count);  // qsv_dist.cu
-int qsv_dist_localize_xmask(qsv_state* s, uint64_t phys_x_mask);          // qsv_dist.cu
+int qsv_dist_localize(qsv_state* s, uint64_t want_local, uint64_t keep);   // qsv_dist.cu
+int qsv_dist_min_lpos(const qsv_state* s);
 
 static uint64_t map_mask(const qsv_state* s, uint64_t logical) {
     uint64_t phys = 0;
@@ -246,6 +247,7 @@ static int phase_selector(double re, double im, int* sel) {
 }
 
 struct TermItem {
+    uint64_t lx, lz;  // logical masks (as given by the caller)
     uint64_t x, z;  // physical masks
     int sel;        // phase selector: phase = (-i)^sel
     int ny;         // number of Y factors: popc(x & z)
@@ -344,6 +346,8 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
         int sel = 0;
         if (phases) QSV_TRY(phase_selector(phases[2 * t], phases[2 * t + 1], &sel));
         TermItem it;
+        it.lx = x_masks[t];
+        it.lz = z_masks[t];
         it.x = map_mask(s, x_masks[t]);
         it.z = map_mask(s, z_masks[t]);
         it.sel = sel;
@@ -497,7 +501,50 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
             slot += g->members.size();
         }
     }
-    if (!direct.empty()) QSV_TRY(run_direct_terms(s, items, direct, d_res, result_slot, slot));
+    if (s->world > 1) {
+        // sharded: a term whose X/Y factors sit on global qubits needs them local first.  Rounds:
+        // evaluate what is ready, then ONE qubit swap for the next batch of terms.
+        const uint64_t local_mask = qsv_local_size(s) - 1;
+        std::vector<size_t> remaining(direct);
+        int g = 0;
+        while ((1 << g) < s->world) ++g;
+        while (!remaining.empty()) {
+            std::vector<size_t> ready, later;
+            for (size_t t : remaining) {
+                items[t].x = map_mask(s, items[t].lx);
+                items[t].z = map_mask(s, items[t].lz);
+                ((items[t].x & ~local_mask) ? later : ready).push_back(t);
+            }
+            if (!ready.empty()) QSV_TRY(run_direct_terms(s, items, ready, d_res, result_slot, slot));
+            remaining.swap(later);
+            if (remaining.empty()) break;
+            // the first waiting term decides; further terms join while their global X qubits fit
+            // in the same swap and enough evictable local qubits remain outside their X masks
+            uint64_t want = 0, keep = 0;
+            auto globals_of = [&](uint64_t lx) {
+                uint64_t w = 0;
+                for (int q = 0; q < s->n; ++q)
+                    if (((lx >> q) & 1ull) && s->perm[q] >= s->n_local) w |= 1ull << q;
+                return w;
+            };
+            auto evictable = [&](uint64_t kp) {
+                int c = 0;
+                for (int q = 0; q < s->n; ++q)
+                    if (s->perm[q] < s->n_local && s->perm[q] >= qsv_dist_min_lpos(s) && !((kp >> q) & 1ull)) ++c;
+                return c;
+            };
+            for (size_t t : remaining) {
+                const uint64_t w2 = want | globals_of(items[t].lx);
+                const uint64_t k2 = keep | items[t].lx;
+                if (want && (__builtin_popcountll(w2) > g || evictable(k2) < __builtin_popcountll(w2))) continue;
+                want = w2;
+                keep = k2;
+            }
+            QSV_TRY(qsv_dist_localize(s, want, keep));
+        }
+    } else if (!direct.empty()) {
+        QSV_TRY(run_direct_terms(s, items, direct, d_res, result_slot, slot));
+    }
 
     if (s->world > 1) QSV_TRY(qsv_dist_allreduce_sum(s, d_res, n_terms));
     QSV_TRY(qsv_ensure_pinned(s, n_terms * sizeof(double)));

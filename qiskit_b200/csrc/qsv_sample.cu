@@ -87,11 +87,18 @@ struct LevelDesc {
 
 #define MAX_LEVELS 5
 
+#define MAX_SHARDS 16
 struct SearchParams {
     ProbSource src;  // level 0
     int nlevels;     // total number of levels including level 0
     LevelDesc lv[MAX_LEVELS];  // lv[k] for k >= 1
     double total;
+    // sharded states: the ranks form one more level above the local trees, chained sequentially:
+    // chain[r] = fl(chain[r-1] + t_{r-1}), chain[0] = 0, total = chain[world]; a uniform belongs to
+    // the first rank r with fl(chain[r+1] / total) > u (clamped) and descends with X = chain[r]
+    int world, rank;
+    uint64_t index_base;
+    double chain[MAX_SHARDS + 1];
 };
 
 // one warp per shot
@@ -104,6 +111,16 @@ __global__ void __launch_bounds__(32 * WARPS_PER_CTA) k_search(SearchParams P, c
         const double u = u_in[sh];
         double X = 0.0;
         uint64_t blk = 0;
+        if (P.world > 1) {
+            int owner = P.world - 1;
+            for (int r = P.world - 2; r >= 0; --r)
+                if (__ddiv_rn(P.chain[r + 1], P.total) > u) owner = r;
+            if (owner != P.rank) {
+                if (lane == 0) out[sh] = 0;
+                continue;
+            }
+            X = P.chain[owner];
+        }
         for (int level = P.nlevels - 1; level >= 1; --level) {
             const double* w = P.lv[level].w + blk * BLK;
             const uint64_t base = blk * BLK;
@@ -144,7 +161,7 @@ __global__ void __launch_bounds__(32 * WARPS_PER_CTA) k_search(SearchParams P, c
         uint64_t nv = P.src.count - base;
         const int last = (int)(nv < BLK ? nv : BLK) - 1;
         if (j > last) j = last;
-        if (lane == 0) out[sh] = base + j;
+        if (lane == 0) out[sh] = (base + j) | P.index_base;
         __syncwarp();
     }
 }
@@ -255,6 +272,8 @@ __global__ void k_collapse(double2* __restrict__ amp, uint64_t groups, GatherBit
 
 // ----------------------------------------------------------------- host ---
 int qsv_dist_canonicalize(qsv_state* s);
+int qsv_dist_allgather(qsv_state* s, const double* dev_in, double* dev_out, size_t count);
+int qsv_dist_allreduce_sum_u64(qsv_state* s, uint64_t* dev_buf, size_t count);
 
 static int resolve_qargs(const qsv_state* s, const int* qargs, int m, GatherBits& G, bool& identity,
                          const char* who) {
@@ -332,11 +351,17 @@ extern "C" int qsv_sample(const qsv_state* cs, const int* qargs, int m, const do
     if (!s || (shots && (!uniforms || !out_indices))) QSV_FAIL(QSV_ERR_INVALID, "qsv_sample: NULL argument");
     if (!qargs) m = s->n;
     QSV_CUDA(cudaSetDevice(s->device));
-    if (s->world > 1) QSV_FAIL(QSV_ERR_UNSUPPORTED, "qsv_sample: sharded states are sampled through qsv_dist_sample");
+    if (s->world > 1) {
+        if (m != s->n) QSV_FAIL(QSV_ERR_UNSUPPORTED, "qsv_sample: sharded states sample all qubits only");
+        for (int j = 0; j < m; ++j)
+            if (qargs && qargs[j] != j) QSV_FAIL(QSV_ERR_UNSUPPORTED, "qsv_sample: sharded states need qargs in order");
+        QSV_TRY(qsv_dist_canonicalize(s));  // the summation tree is defined on the identity layout
+    }
     GatherBits G;
     bool identity;
     QSV_TRY(resolve_qargs(s, qargs, m, G, identity, "qsv_sample"));
-    const uint64_t outs = 1ull << m;
+    if (s->world > 1) identity = true;
+    const uint64_t outs = s->world > 1 ? qsv_local_size(s) : 1ull << m;
     // scratch layout: [marginal probs (if any)] [level totals / prefixes ...] [uniforms] [indices]
     uint64_t nblk[MAX_LEVELS + 1];
     int nlevels = 1;
@@ -353,6 +378,7 @@ extern "C" int qsv_sample(const qsv_state* cs, const int* qargs, int m, const do
     size_t o_tot[MAX_LEVELS + 1], o_w[MAX_LEVELS + 1];
     for (int k = 0; k < nlevels; ++k) o_tot[k] = take(nblk[k] * sizeof(double));  // totals of level-k blocks
     for (int k = 1; k < nlevels; ++k) o_w[k] = take(nblk[k] * BLK * sizeof(double));
+    size_t o_all = take(MAX_SHARDS * sizeof(double));
     size_t o_u = take(shots * sizeof(double));
     size_t o_idx = take(shots * sizeof(uint64_t));
     QSV_TRY(qsv_ensure_scratch(s, off + 256));
@@ -395,7 +421,24 @@ extern "C" int qsv_sample(const qsv_state* cs, const int* qargs, int m, const do
     QSV_TRY(qsv_ensure_pinned(s, 64));
     QSV_CUDA(cudaMemcpyAsync(s->pinned, base + o_tot[nlevels - 1], sizeof(double), cudaMemcpyDeviceToHost, s->stream));
     QSV_CUDA(cudaStreamSynchronize(s->stream));
-    const double total = *(const double*)s->pinned;
+    double total = *(const double*)s->pinned;
+    if (s->world > 1) {
+        double* d_tot = (double*)(base + o_tot[nlevels - 1]);
+        double* d_all = (double*)(base + o_all);
+        QSV_TRY(qsv_dist_allgather(s, d_tot, d_all, 1));
+        double tot[MAX_SHARDS];
+        QSV_CUDA(cudaMemcpyAsync(s->pinned, d_all, s->world * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+        QSV_CUDA(cudaStreamSynchronize(s->stream));
+        memcpy(tot, s->pinned, s->world * sizeof(double));
+        P.world = s->world;
+        P.rank = s->rank;
+        P.index_base = (uint64_t)s->rank << s->n_local;
+        P.chain[0] = 0.0;
+        for (int r = 0; r < s->world; ++r) P.chain[r + 1] = r == 0 ? tot[0] : P.chain[r] + tot[r];
+        total = P.chain[s->world];
+    } else {
+        P.world = 1;
+    }
     if (total_out) *total_out = total;
     if (shots == 0) return QSV_OK;
     if (!(total > 0.0)) QSV_FAIL(QSV_ERR_INVALID, "qsv_sample: probabilities sum to %g", total);
@@ -411,6 +454,7 @@ extern "C" int qsv_sample(const qsv_state* cs, const int* qargs, int m, const do
         QSV_CUDA(cudaGetLastError());
         s->ctr.kernel_launches++;
     }
+    if (s->world > 1) QSV_TRY(qsv_dist_allreduce_sum_u64(s, (uint64_t*)(base + o_idx), shots));
     QSV_CUDA(cudaMemcpyAsync(out_indices, base + o_idx, shots * sizeof(uint64_t), cudaMemcpyDeviceToHost, s->stream));
     QSV_CUDA(cudaStreamSynchronize(s->stream));
     s->ctr.d2h_bytes += shots * sizeof(uint64_t);

@@ -130,6 +130,7 @@ extern "C" int qsv_create(qsv_state** out, int n_qubits, int device) {
 }
 
 void qsv_dist_free(qsv_state* s);  // qsv_dist.cu
+int qsv_dist_set_option(qsv_state* s, const char* name, int64_t value);
 
 extern "C" int qsv_destroy(qsv_state* s) {
     if (!s) return QSV_OK;
@@ -288,6 +289,8 @@ extern "C" int qsv_set_option(qsv_state* s, const char* name, int64_t value) {
         s->use_direct = value != 0;
     } else if (!strcmp(name, "use_cluster")) {
         s->use_cluster = value != 0;
+    } else if (!strncmp(name, "dist_", 5)) {
+        return qsv_dist_set_option(s, name, value);
     } else {
         QSV_FAIL(QSV_ERR_INVALID, "qsv_set_option: unknown option '%s'", name);
     }

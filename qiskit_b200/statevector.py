@@ -73,7 +73,10 @@ class Statevector:
         h, self._h = getattr(self, "_h", None), None
         if h is not None:
             try:
-                _lib.release(h, self._n, self._device)
+                if getattr(self, "_sharded", None):      # sharded handles own an NCCL communicator
+                    _lib.load().qsv_destroy(h)
+                else:
+                    _lib.release(h, self._n, self._device)
             except Exception:  # noqa: BLE001 - interpreter shutdown
                 pass
 
