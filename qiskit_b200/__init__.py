@@ -16,6 +16,17 @@ from .primitives import BitArray, StatevectorEstimator, StatevectorSampler
 __all__ = [
     "QiskitError", "QuantumCircuit", "ClassicalRegister", "Parameter", "ParameterVector", "Gate",
     "Instruction", "Pauli", "PauliList", "SparsePauliOp", "Statevector", "StatevectorEstimator",
-    "StatevectorSampler", "BitArray",
+    "StatevectorSampler", "BitArray", "install",
 ]
 __version__ = "0.1.0"
+
+
+def install():
+    """Opt-in: rebind Qiskit's statevector entry points to the device classes (SURVEY 8b B2 iii).
+    Only meaningful where ``import qiskit`` works; raises ImportError otherwise."""
+    import qiskit.primitives as _prims          # noqa: PLC0415 - optional dependency
+    import qiskit.quantum_info as _qi
+
+    _prims.StatevectorEstimator = StatevectorEstimator
+    _prims.StatevectorSampler = StatevectorSampler
+    _qi.Statevector = Statevector
