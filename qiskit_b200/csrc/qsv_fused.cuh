@@ -1,0 +1,326 @@
+// k_fused_pass: the fused-pass kernel (second generation of k_cluster_pass, qsv_gate.cu).
+//
+// ncu on k_cluster_pass (profiles/r1_ncu_cluster.txt) showed 8 resident warps per SM stalled on
+// the tile load, 145-245 thread instructions per amplitude of which only 32 were FP64 (64
+// register moves per sub-op from the dynamic dispatch, per-thread loads of uniform descriptors,
+// bit-by-bit index arithmetic) and instruction-cache misses.  This kernel keeps the idea -- a
+// pass = tile of 2^12 amplitudes in shared memory, cut into phases that work on 4 "register
+// bits" -- and changes the execution model:
+//   * persistent CTAs (one per SM, 256 threads, 16 amplitudes per thread) walk the tiles with a
+//     two-deep cp.async pipeline: tile i+1 streams into the second buffer while tile i computes;
+//   * everything uniform (phase and sub-op descriptors, gate matrices) lives in the kernel
+//     parameter (constant bank), everything per-thread (slot of the thread in a phase, phase-table
+//     index of a diagonal op) is a 16-bit table built on the host and cached in shared memory;
+//   * permutation gates (CX, SWAP, X, CCX, ...) are never executed: a phase is
+//     [permutations] [dense / diagonal ops] [permutations] and the permutations are folded into
+//     the shared-memory slot each register is read from / written to (16 XOR masks per phase);
+//   * dense ops update the register file in place (no copies across the dispatch loop);
+//   * when the last phase leaves the four lowest tile bits to the threads, registers are stored
+//     straight to global memory (256-byte runs) instead of through shared memory.
+#pragma once
+
+#include "qsv_common.cuh"
+
+#define FP_T 12
+#define FP_NT 256
+#define FP_TILE (1 << FP_T)
+#define FP_MAX_PHASES 12
+#define FP_MAX_SUBS 112
+#define FP_MAX_MAT 1408  // doubles of matrix data per pass
+#define FP_MAX_TABS 40   // per-thread u16 tables (one per phase + one per diagonal op)
+#define FP_NOCOEF 0xffffffffu
+
+enum { FP_D1C = 0, FP_D1R = 1, FP_D2C = 2, FP_D2R = 3, FP_DIAG = 4 };
+
+struct FpPhase {           // 80 bytes
+    uint16_t rd[16];       // register r is read from slot (thread slot ^ rd[r])
+    uint16_t wr[16];       // ... and written to slot (thread slot ^ wr[r])
+    uint32_t rcoef, wcoef; // 16 complex factors applied after the read / before the write (gdata offset)
+    uint16_t sub_first;
+    uint8_t nsub;
+    uint8_t direct;        // 1: registers go straight to global memory (last phase only)
+    uint16_t tab;          // per-thread table: swizzled slot of the thread in this phase
+    uint16_t pad;
+};
+
+struct FpSub {             // 8 bytes
+    uint8_t kind;          // FP_*
+    uint8_t b;             // register bits: b0 | b1 << 2 (ascending)
+    uint16_t mat;          // offset into mats (doubles); FP_DIAG: index into diags
+    uint32_t pad;
+};
+
+struct FpDiag {            // 64 bytes, global memory
+    uint32_t table_off;    // into gdata (double2 units)
+    uint16_t tab;          // per-thread table: table index bits contributed by the thread
+    uint8_t nglob;         // table index bits fed by index bits outside the tile
+    uint8_t all_same;      // 1: no register bit feeds the table (one lookup per thread)
+    uint16_t regpart[16];  // table index bits contributed by register r
+    uint8_t gbit[10];      // global index bit ...
+    uint8_t gj[10];        // ... feeding table index bit gj
+    uint32_t pad;
+};
+static_assert(sizeof(FpDiag) == 64, "FpDiag layout");
+
+struct FpPass {
+    uint64_t index_base;   // sharded states: rank << n_local
+    uint32_t ntiles;
+    int32_t nphases;
+    int32_t ntabs;
+    int32_t pos[FP_T];     // ascending global bit position of tile bit b
+    const uint16_t* tabs;  // [ntabs][256]
+    const FpDiag* diags;
+    const double2* gdata;  // diagonal tables and coefficient vectors
+    uint64_t st_off[16];   // direct store: global offset of register r
+    uint8_t st_tpos[8];    // direct store: tile bit of thread bit j
+    FpPhase phases[FP_MAX_PHASES];
+    FpSub subs[FP_MAX_SUBS];
+    double mats[FP_MAX_MAT];
+};
+
+__host__ __device__ __forceinline__ uint32_t fp_swz(uint32_t i) {
+    return i ^ (((i >> 3) ^ (i >> 6) ^ (i >> 9)) & 7u);
+}
+
+// ---- dense ops on the 16 registers of a thread, in place --------------------------------
+template <int B>
+__device__ __forceinline__ void fp_d1c(double2 (&v)[16], const FpPass& P, int mo) {
+    const double m00r = P.mats[mo + 0], m00i = P.mats[mo + 1], m01r = P.mats[mo + 2], m01i = P.mats[mo + 3];
+    const double m10r = P.mats[mo + 4], m10i = P.mats[mo + 5], m11r = P.mats[mo + 6], m11i = P.mats[mo + 7];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        if (i & (1 << B)) continue;
+        const double2 a0 = v[i], a1 = v[i | (1 << B)];
+        double tr = m00r * a0.x;
+        tr = fma(-m00i, a0.y, tr);
+        tr = fma(m01r, a1.x, tr);
+        tr = fma(-m01i, a1.y, tr);
+        double ti = m00r * a0.y;
+        ti = fma(m00i, a0.x, ti);
+        ti = fma(m01r, a1.y, ti);
+        ti = fma(m01i, a1.x, ti);
+        double ur = m10r * a0.x;
+        ur = fma(-m10i, a0.y, ur);
+        ur = fma(m11r, a1.x, ur);
+        ur = fma(-m11i, a1.y, ur);
+        double ui = m10r * a0.y;
+        ui = fma(m10i, a0.x, ui);
+        ui = fma(m11r, a1.y, ui);
+        ui = fma(m11i, a1.x, ui);
+        v[i] = make_double2(tr, ti);
+        v[i | (1 << B)] = make_double2(ur, ui);
+    }
+}
+
+template <int B>
+__device__ __forceinline__ void fp_d1r(double2 (&v)[16], const FpPass& P, int mo) {
+    const double m00 = P.mats[mo + 0], m01 = P.mats[mo + 1], m10 = P.mats[mo + 2], m11 = P.mats[mo + 3];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        if (i & (1 << B)) continue;
+        const double2 a0 = v[i], a1 = v[i | (1 << B)];
+        v[i] = make_double2(fma(m01, a1.x, m00 * a0.x), fma(m01, a1.y, m00 * a0.y));
+        v[i | (1 << B)] = make_double2(fma(m11, a1.x, m10 * a0.x), fma(m11, a1.y, m10 * a0.y));
+    }
+}
+
+template <int B0, int B1>
+__device__ __forceinline__ void fp_d2c(double2 (&v)[16], const FpPass& P, int mo) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        if (i & ((1 << B0) | (1 << B1))) continue;
+        const double2 a[4] = {v[i], v[i | (1 << B0)], v[i | (1 << B1)], v[i | (1 << B0) | (1 << B1)]};
+        double2 o[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            double re = 0.0, im = 0.0;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const double mr = P.mats[mo + 8 * r + 2 * c], mi = P.mats[mo + 8 * r + 2 * c + 1];
+                if (c == 0) {
+                    re = mr * a[0].x;
+                    im = mr * a[0].y;
+                } else {
+                    re = fma(mr, a[c].x, re);
+                    im = fma(mr, a[c].y, im);
+                }
+                re = fma(-mi, a[c].y, re);
+                im = fma(mi, a[c].x, im);
+            }
+            o[r] = make_double2(re, im);
+        }
+        v[i] = o[0];
+        v[i | (1 << B0)] = o[1];
+        v[i | (1 << B1)] = o[2];
+        v[i | (1 << B0) | (1 << B1)] = o[3];
+    }
+}
+
+template <int B0, int B1>
+__device__ __forceinline__ void fp_d2r(double2 (&v)[16], const FpPass& P, int mo) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        if (i & ((1 << B0) | (1 << B1))) continue;
+        const double2 a[4] = {v[i], v[i | (1 << B0)], v[i | (1 << B1)], v[i | (1 << B0) | (1 << B1)]};
+        double2 o[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const double m0 = P.mats[mo + 4 * r], m1 = P.mats[mo + 4 * r + 1], m2 = P.mats[mo + 4 * r + 2],
+                         m3 = P.mats[mo + 4 * r + 3];
+            o[r] = make_double2(fma(m3, a[3].x, fma(m2, a[2].x, fma(m1, a[1].x, m0 * a[0].x))),
+                                fma(m3, a[3].y, fma(m2, a[2].y, fma(m1, a[1].y, m0 * a[0].y))));
+        }
+        v[i] = o[0];
+        v[i | (1 << B0)] = o[1];
+        v[i | (1 << B1)] = o[2];
+        v[i | (1 << B0) | (1 << B1)] = o[3];
+    }
+}
+
+__device__ __forceinline__ void fp_diag(double2 (&v)[16], const FpPass& P, int di, const uint16_t* __restrict__ tabs_sm,
+                                        uint64_t tile_base) {
+    const FpDiag* __restrict__ d = P.diags + di;
+    const uint4 w0 = __ldg(reinterpret_cast<const uint4*>(d));  // table_off, tab|nglob|all_same, regpart[0..3]
+    uint32_t thr = tabs_sm[(w0.y & 0xffffu) * FP_NT + threadIdx.x];
+    const int nglob = (w0.y >> 16) & 255;
+    for (int j = 0; j < nglob; ++j) thr |= (uint32_t)((tile_base >> d->gbit[j]) & 1ull) << d->gj[j];
+    const double2* __restrict__ tab = P.gdata + w0.x + thr;
+    if ((w0.y >> 24) & 1u) {
+        const double2 c = __ldg(tab);
+#pragma unroll
+        for (int r = 0; r < 16; ++r) v[r] = cmul(v[r], c);
+    } else {
+#pragma unroll
+        for (int r = 0; r < 16; ++r) v[r] = cmul(v[r], __ldg(tab + d->regpart[r]));
+    }
+}
+
+__device__ __forceinline__ void fp_apply(double2 (&v)[16], const FpPass& P, int si, const uint16_t* __restrict__ tabs_sm,
+                                         uint64_t tile_base) {
+    const int kind = P.subs[si].kind, b = P.subs[si].b, mo = P.subs[si].mat;
+    switch (kind * 16 + b) {
+        case FP_D1C * 16 + 0: fp_d1c<0>(v, P, mo); break;
+        case FP_D1C * 16 + 1: fp_d1c<1>(v, P, mo); break;
+        case FP_D1C * 16 + 2: fp_d1c<2>(v, P, mo); break;
+        case FP_D1C * 16 + 3: fp_d1c<3>(v, P, mo); break;
+        case FP_D1R * 16 + 0: fp_d1r<0>(v, P, mo); break;
+        case FP_D1R * 16 + 1: fp_d1r<1>(v, P, mo); break;
+        case FP_D1R * 16 + 2: fp_d1r<2>(v, P, mo); break;
+        case FP_D1R * 16 + 3: fp_d1r<3>(v, P, mo); break;
+        case FP_D2C * 16 + 4: fp_d2c<0, 1>(v, P, mo); break;
+        case FP_D2C * 16 + 8: fp_d2c<0, 2>(v, P, mo); break;
+        case FP_D2C * 16 + 12: fp_d2c<0, 3>(v, P, mo); break;
+        case FP_D2C * 16 + 9: fp_d2c<1, 2>(v, P, mo); break;
+        case FP_D2C * 16 + 13: fp_d2c<1, 3>(v, P, mo); break;
+        case FP_D2C * 16 + 14: fp_d2c<2, 3>(v, P, mo); break;
+        case FP_D2R * 16 + 4: fp_d2r<0, 1>(v, P, mo); break;
+        case FP_D2R * 16 + 8: fp_d2r<0, 2>(v, P, mo); break;
+        case FP_D2R * 16 + 12: fp_d2r<0, 3>(v, P, mo); break;
+        case FP_D2R * 16 + 9: fp_d2r<1, 2>(v, P, mo); break;
+        case FP_D2R * 16 + 13: fp_d2r<1, 3>(v, P, mo); break;
+        case FP_D2R * 16 + 14: fp_d2r<2, 3>(v, P, mo); break;
+        default: fp_diag(v, P, mo, tabs_sm, tile_base); break;
+    }
+}
+
+// dynamic smem: [2][4096] double2 tile buffers, then [ntabs][256] u16 tables
+__global__ void __launch_bounds__(FP_NT, 1) k_fused_pass(double2* __restrict__ amp, const __grid_constant__ FpPass P) {
+    extern __shared__ __align__(16) unsigned char fp_smem[];
+    double2* const buf0 = reinterpret_cast<double2*>(fp_smem);
+    uint16_t* const tabs_sm = reinterpret_cast<uint16_t*>(fp_smem + 2 * FP_TILE * sizeof(double2));
+    const uint32_t t = threadIdx.x;
+
+    for (int i = t; i < P.ntabs * (FP_NT / 2); i += FP_NT)   // two u16 per word
+        reinterpret_cast<uint32_t*>(tabs_sm)[i] = __ldg(reinterpret_cast<const uint32_t*>(P.tabs) + i);
+
+    // global offset of this thread's element of a 256-element row (copy-in / copy-out mapping)
+    uint64_t cp_off = 0;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) cp_off |= (uint64_t)((t >> b) & 1u) << P.pos[b];
+    uint64_t row_off[16];
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+        uint64_t o = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            if ((r >> j) & 1) o |= 1ull << P.pos[8 + j];
+        row_off[r] = o;
+    }
+    const uint32_t st = fp_swz(t);
+    // direct-store mapping of the last phase
+    uint64_t st_thread = 0;
+#pragma unroll
+    for (int b = 0; b < 8; ++b) st_thread |= (uint64_t)((t >> b) & 1u) << P.pos[P.st_tpos[b]];
+
+    auto tile_base_of = [&](uint32_t tile) {
+        uint64_t base = tile;
+#pragma unroll
+        for (int b = 0; b < FP_T; ++b) base = insert_zero(base, P.pos[b]);
+        return base;
+    };
+    auto issue_load = [&](uint32_t tile, double2* buf) {
+        const double2* __restrict__ g = amp + tile_base_of(tile) + cp_off;
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(buf + (st ^ fp_swz((uint32_t)r << 8)));
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(g + row_off[r]));
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+
+    uint32_t tile = blockIdx.x;
+    if (tile < P.ntiles) issue_load(tile, buf0);
+    int cur = 0;
+    __syncthreads();  // tables visible
+    for (; tile < P.ntiles; tile += gridDim.x, cur ^= 1) {
+        double2* const tilebuf = buf0 + cur * FP_TILE;
+        const uint32_t next = tile + gridDim.x;
+        if (next < P.ntiles) {
+            issue_load(next, buf0 + (cur ^ 1) * FP_TILE);
+            asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        }
+        __syncthreads();
+        const uint64_t tile_base = tile_base_of(tile);
+        const uint64_t diag_base = tile_base | P.index_base;
+        bool stored = false;
+#pragma unroll 1
+        for (int p = 0; p < P.nphases; ++p) {
+            const FpPhase& ph = P.phases[p];
+            const uint32_t sb = tabs_sm[ph.tab * FP_NT + t];
+            double2 v[16];
+#pragma unroll
+            for (int r = 0; r < 16; ++r) v[r] = tilebuf[sb ^ ph.rd[r]];
+            if (ph.rcoef != FP_NOCOEF) {
+                const double2* __restrict__ c = P.gdata + ph.rcoef;
+#pragma unroll
+                for (int r = 0; r < 16; ++r) v[r] = cmul(__ldg(c + r), v[r]);
+            }
+            const int s0 = ph.sub_first, s1 = s0 + ph.nsub;
+#pragma unroll 1
+            for (int si = s0; si < s1; ++si) fp_apply(v, P, si, tabs_sm, diag_base);
+            if (ph.wcoef != FP_NOCOEF) {
+                const double2* __restrict__ c = P.gdata + ph.wcoef;
+#pragma unroll
+                for (int r = 0; r < 16; ++r) v[r] = cmul(__ldg(c + r), v[r]);
+            }
+            if (ph.direct) {
+                double2* __restrict__ g = amp + tile_base + st_thread;
+#pragma unroll
+                for (int r = 0; r < 16; ++r) g[P.st_off[r]] = v[r];
+                stored = true;
+            } else {
+#pragma unroll
+                for (int r = 0; r < 16; ++r) tilebuf[sb ^ ph.wr[r]] = v[r];
+            }
+            __syncthreads();
+        }
+        if (!stored) {
+            double2* __restrict__ g = amp + tile_base + cp_off;
+#pragma unroll
+            for (int r = 0; r < 16; ++r) g[row_off[r]] = tilebuf[st ^ fp_swz((uint32_t)r << 8)];
+            __syncthreads();
+        }
+    }
+}

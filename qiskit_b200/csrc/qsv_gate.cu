@@ -13,6 +13,7 @@
 #include <complex>
 
 #include "qsv_common.cuh"
+#include "qsv_fused.cuh"
 
 // ------------------------------------------------------------ device ops --
 enum {
@@ -1378,6 +1379,327 @@ static int launch_cluster_pass(qsv_state* s, const ClPass& P, uint64_t ntiles) {
     return QSV_OK;
 }
 
+// ---- fused pass (k_fused_pass, qsv_fused.cuh): host side -------------------------------------
+struct FusedBuilt {
+    FpPass P;
+    size_t tabs_off, diags_off, gdata_off;
+};
+
+// Build the descriptors of one fused pass.  `ok` = false when the pass does not fit the kernel's
+// fixed capacities (the caller falls back to k_cluster_pass).
+static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const PassPlan& plan,
+                            std::vector<char>& stage, FusedBuilt& out, bool& ok) {
+    ok = false;
+    const int n = s->n_local;
+    if (n < FP_T) return QSV_OK;
+    uint64_t active = plan.qmask;
+    for (int b = 0; b < n && popc64(active) < FP_T; ++b) active |= 1ull << b;  // low bits first
+    if (popc64(active) != FP_T) return QSV_OK;
+    FpPass& P = out.P;
+    memset(&P, 0, sizeof P);
+    int local_of[64];
+    for (int b = 0, t = 0; b < 64; ++b) {
+        local_of[b] = -1;
+        if ((active >> b) & 1ull) {
+            P.pos[t] = b;
+            local_of[b] = t++;
+        }
+    }
+    std::vector<TileOp> ops;
+    QSV_TRY(make_tile_ops(gates, plan, local_of, ops));
+
+    // ---- phase selection: [leading permutations][dense / diagonal][trailing permutations]
+    struct PhaseSel {
+        uint32_t S;
+        std::vector<int> sel;
+        std::vector<char> role;  // 0 mid, 1 leading permutation, 2 trailing permutation
+    };
+    std::vector<PhaseSel> sels;
+    {
+        std::vector<char> done(ops.size(), 0);
+        size_t ndone = 0;
+        while (ndone < ops.size()) {
+            PhaseSel ps;
+            ps.S = 0;
+            uint32_t blocked = 0;
+            int state[FP_T];  // per tile bit: 0 untouched, 1 dense/diag seen, 2 closed by a trailing permutation
+            for (int b = 0; b < FP_T; ++b) state[b] = 0;
+            for (size_t i = 0; i < ops.size(); ++i) {
+                if (done[i]) continue;
+                uint32_t m = 0;
+                for (int j = 0; j < ops[i].k; ++j)
+                    if (ops[i].bits[j] < 64) m |= 1u << ops[i].bits[j];
+                if (m & blocked) {
+                    blocked |= m;
+                    continue;
+                }
+                bool closed = false, fresh = true;
+                for (int b = 0; b < FP_T; ++b)
+                    if ((m >> b) & 1u) {
+                        closed |= state[b] == 2;
+                        fresh &= state[b] == 0;
+                    }
+                char role = 0;
+                if (ops[i].kind == CL_DIAG) {
+                    if (closed) {
+                        blocked |= m;
+                        continue;
+                    }
+                    for (int b = 0; b < FP_T; ++b)
+                        if (((m >> b) & 1u) && state[b] == 0) state[b] = 1;
+                } else {
+                    if (__builtin_popcount(ps.S | m) > 4 || (ops[i].kind != CL_MONO && closed)) {
+                        blocked |= m;
+                        continue;
+                    }
+                    ps.S |= m;
+                    if (ops[i].kind == CL_MONO) {
+                        role = fresh ? 1 : 2;
+                        if (role == 2)
+                            for (int b = 0; b < FP_T; ++b)
+                                if ((m >> b) & 1u) state[b] = 2;
+                    } else {
+                        for (int b = 0; b < FP_T; ++b)
+                            if ((m >> b) & 1u) state[b] = 1;
+                    }
+                }
+                ps.sel.push_back((int)i);
+                ps.role.push_back(role);
+                done[i] = 1;
+                ++ndone;
+            }
+            for (int b = FP_T - 1; b >= 0 && __builtin_popcount(ps.S) < 4; --b) ps.S |= 1u << b;
+            sels.push_back(std::move(ps));
+        }
+    }
+    if (sels.empty() || sels.size() > FP_MAX_PHASES) return QSV_OK;
+
+    std::vector<uint16_t> tabs;
+    std::vector<FpDiag> diags;
+    std::vector<double2> gdata;
+    int nsubs = 0, nmat = 0;
+    bool low4 = true;  // tile bits 0..3 are index bits 0..3 (contiguous 256-byte runs)
+    for (int b = 0; b < 4; ++b) low4 &= (P.pos[b] == b);
+
+    for (size_t pi = 0; pi < sels.size(); ++pi) {
+        const PhaseSel& ps = sels[pi];
+        const uint32_t S = ps.S;
+        FpPhase& ph = P.phases[pi];
+        int rpos[4];
+        for (int b = 0, j = 0; b < FP_T; ++b)
+            if ((S >> b) & 1u) rpos[j++] = b;
+        const bool direct = (pi + 1 == sels.size()) && low4 && !(S & 15u) && s->use_direct_store;
+        // thread bits
+        int tpos[8], nt = 0;
+        uint32_t rest = ((1u << FP_T) - 1u) & ~S;
+        if (!direct) {
+            // lanes 0..2 on three tile bits with distinct (bit mod 3): a quarter-warp's 16-byte
+            // accesses then fall into distinct swizzled columns
+            for (int c = 0; c < 3; ++c)
+                for (int b = 0; b < FP_T; ++b)
+                    if (((rest >> b) & 1u) && b % 3 == c) {
+                        tpos[nt++] = b;
+                        rest &= ~(1u << b);
+                        break;
+                    }
+        }
+        for (int b = 0; b < FP_T; ++b)
+            if ((rest >> b) & 1u) tpos[nt++] = b;
+        if (nt != 8) QSV_FAIL(QSV_ERR_UNSUPPORTED, "internal: fused pass thread bits");
+        uint16_t base_of[FP_NT];
+        for (int t = 0; t < FP_NT; ++t) {
+            uint32_t base = 0;
+            for (int j = 0; j < 8; ++j) base |= (uint32_t)((t >> j) & 1) << tpos[j];
+            base_of[t] = (uint16_t)base;
+        }
+        if (tabs.size() / FP_NT >= FP_MAX_TABS) return QSV_OK;
+        ph.tab = (uint16_t)(tabs.size() / FP_NT);
+        for (int t = 0; t < FP_NT; ++t) tabs.push_back((uint16_t)fp_swz(base_of[t]));
+        auto slot_mask = [&](int nib) {
+            uint32_t m = 0;
+            for (int j = 0; j < 4; ++j)
+                if ((nib >> j) & 1) m ^= fp_swz(1u << rpos[j]);
+            return (uint16_t)m;
+        };
+        // compose the leading / trailing permutations into one map of the 16 register slots
+        auto compose = [&](int which, int* src16, cplx* c16) {
+            bool any = false;
+            for (int r = 0; r < 16; ++r) {
+                src16[r] = r;
+                c16[r] = cplx(1.0, 0.0);
+            }
+            for (size_t i = 0; i < ps.sel.size(); ++i) {
+                if (ps.role[i] != which) continue;
+                any = true;
+                const TileOp& op = ops[ps.sel[i]];
+                int rb[3];
+                for (int j = 0; j < op.k; ++j) rb[j] = rank_in(S, op.bits[j]);
+                int nsrc[16];
+                cplx nc[16];
+                for (int r = 0; r < 16; ++r) {
+                    int rr = 0;
+                    for (int j = 0; j < op.k; ++j) rr |= ((r >> rb[j]) & 1) << j;
+                    int x = r;
+                    for (int j = 0; j < op.k; ++j) x = (x & ~(1 << rb[j])) | (((op.src[rr] >> j) & 1) << rb[j]);
+                    nsrc[r] = src16[x];
+                    nc[r] = op.m[rr] * c16[x];
+                }
+                memcpy(src16, nsrc, sizeof nsrc);
+                for (int r = 0; r < 16; ++r) c16[r] = nc[r];
+            }
+            return any;
+        };
+        int src16[16], dst16[16];
+        cplx c16[16];
+        ph.rcoef = ph.wcoef = FP_NOCOEF;
+        compose(1, src16, c16);  // v[r] = c[r] * slot[src[r]]
+        {
+            bool unit = true;
+            for (int r = 0; r < 16; ++r) {
+                ph.rd[r] = slot_mask(src16[r]);
+                unit &= (c16[r] == cplx(1.0, 0.0));
+            }
+            if (!unit) {
+                ph.rcoef = (uint32_t)gdata.size();
+                for (int r = 0; r < 16; ++r) gdata.push_back(make_double2(c16[r].real(), c16[r].imag()));
+            }
+        }
+        compose(2, src16, c16);  // slot[r] = c[r] * v[src[r]]: register q = src[r] goes to slot r
+        {
+            bool unit = true;
+            cplx cq[16];
+            for (int r = 0; r < 16; ++r) {
+                dst16[src16[r]] = r;
+                cq[src16[r]] = c16[r];
+                unit &= (c16[r] == cplx(1.0, 0.0));
+            }
+            for (int q = 0; q < 16; ++q) ph.wr[q] = slot_mask(dst16[q]);
+            if (!unit) {
+                ph.wcoef = (uint32_t)gdata.size();
+                for (int q = 0; q < 16; ++q) gdata.push_back(make_double2(cq[q].real(), cq[q].imag()));
+            }
+        }
+        ph.direct = direct ? 1 : 0;
+        if (direct) {
+            for (int j = 0; j < 8; ++j) P.st_tpos[j] = (uint8_t)tpos[j];
+            for (int q = 0; q < 16; ++q) {
+                uint64_t off = 0;
+                for (int j = 0; j < 4; ++j)
+                    if ((dst16[q] >> j) & 1) off |= 1ull << P.pos[rpos[j]];
+                P.st_off[q] = off;
+            }
+        }
+        ph.sub_first = (uint16_t)nsubs;
+        int cnt = 0;
+        for (size_t i = 0; i < ps.sel.size(); ++i) {
+            if (ps.role[i]) continue;
+            const TileOp& op = ops[ps.sel[i]];
+            if (nsubs >= FP_MAX_SUBS || cnt >= 255) return QSV_OK;
+            FpSub& sb = P.subs[nsubs];
+            memset(&sb, 0, sizeof sb);
+            if (op.kind == CL_DIAG) {
+                if (tabs.size() / FP_NT >= FP_MAX_TABS || diags.size() >= 65535) return QSV_OK;
+                FpDiag d;
+                memset(&d, 0, sizeof d);
+                d.table_off = (uint32_t)gdata.size();
+                d.tab = (uint16_t)(tabs.size() / FP_NT);
+                bool any_reg = false;
+                uint32_t tmask_bits[DIAG_MAX_BITS];
+                for (int j = 0; j < op.k; ++j) {
+                    tmask_bits[j] = 0xffffffffu;
+                    if (op.bits[j] >= 64) {
+                        d.gbit[d.nglob] = (uint8_t)(op.bits[j] - 64);
+                        d.gj[d.nglob] = (uint8_t)j;
+                        ++d.nglob;
+                    } else if ((S >> op.bits[j]) & 1u) {
+                        any_reg = true;
+                    } else {
+                        tmask_bits[j] = (uint32_t)op.bits[j];
+                    }
+                }
+                for (int r = 0; r < 16; ++r) {
+                    uint32_t roff = 0;
+                    for (int j = 0; j < 4; ++j) roff |= (uint32_t)((r >> j) & 1) << rpos[j];
+                    uint32_t part = 0;
+                    for (int j = 0; j < op.k; ++j)
+                        if (op.bits[j] < 64 && ((S >> op.bits[j]) & 1u)) part |= ((roff >> op.bits[j]) & 1u) << j;
+                    d.regpart[r] = (uint16_t)part;
+                }
+                d.all_same = any_reg ? 0 : 1;
+                for (int t = 0; t < FP_NT; ++t) {
+                    uint32_t thr = 0;
+                    for (int j = 0; j < op.k; ++j)
+                        if (tmask_bits[j] != 0xffffffffu) thr |= ((base_of[t] >> tmask_bits[j]) & 1u) << j;
+                    tabs.push_back((uint16_t)thr);
+                }
+                for (const cplx& v : op.m) gdata.push_back(make_double2(v.real(), v.imag()));
+                sb.kind = FP_DIAG;
+                sb.mat = (uint16_t)diags.size();
+                diags.push_back(d);
+            } else {
+                // canonical order: register bits ascending; order[j'] = matrix bit feeding canonical bit j'
+                int rb[2], order[2] = {0, 1};
+                for (int j = 0; j < op.k; ++j) rb[j] = rank_in(S, op.bits[j]);
+                if (op.k == 2 && rb[0] > rb[1]) std::swap(order[0], order[1]);
+                const int dim = 1 << op.k;
+                auto to_orig = [&](int rc) {
+                    int r = 0;
+                    for (int j = 0; j < op.k; ++j) r |= ((rc >> j) & 1) << order[j];
+                    return r;
+                };
+                const bool real = op.kind == CL_DENSE1R || op.kind == CL_DENSE2R;
+                const int need = dim * dim * (real ? 1 : 2);
+                if (nmat + need > FP_MAX_MAT) return QSV_OK;
+                sb.kind = op.k == 1 ? (real ? FP_D1R : FP_D1C) : (real ? FP_D2R : FP_D2C);
+                sb.b = op.k == 1 ? (uint8_t)rb[0] : (uint8_t)(rb[order[0]] | (rb[order[1]] << 2));
+                sb.mat = (uint16_t)nmat;
+                for (int rc = 0; rc < dim; ++rc)
+                    for (int cc = 0; cc < dim; ++cc) {
+                        const cplx v = op.m[(size_t)to_orig(rc) * dim + to_orig(cc)];
+                        P.mats[nmat++] = v.real();
+                        if (!real) P.mats[nmat++] = v.imag();
+                    }
+            }
+            ++nsubs;
+            ++cnt;
+        }
+        ph.nsub = (uint8_t)cnt;
+    }
+    P.nphases = (int)sels.size();
+    P.ntabs = (int)(tabs.size() / FP_NT);
+    P.ntiles = (uint32_t)(1ull << (n - FP_T));
+    P.index_base = s->world > 1 ? ((uint64_t)s->rank << s->n_local) : 0;
+    const size_t tabs_bytes = tabs.size() * sizeof(uint16_t);
+    const size_t diag_bytes = diags.size() * sizeof(FpDiag);
+    const size_t gdata_bytes = gdata.size() * sizeof(double2);
+    out.tabs_off = (stage.size() + 63) & ~(size_t)63;
+    out.diags_off = (out.tabs_off + tabs_bytes + 63) & ~(size_t)63;
+    out.gdata_off = (out.diags_off + diag_bytes + 63) & ~(size_t)63;
+    stage.resize(out.gdata_off + gdata_bytes);
+    memcpy(stage.data() + out.tabs_off, tabs.data(), tabs_bytes);
+    if (diag_bytes) memcpy(stage.data() + out.diags_off, diags.data(), diag_bytes);
+    if (gdata_bytes) memcpy(stage.data() + out.gdata_off, gdata.data(), gdata_bytes);
+    s->ctr.phases += sels.size();
+    ok = true;
+    return QSV_OK;
+}
+
+static int launch_fused_pass(qsv_state* s, const FpPass& P) {
+    const size_t smem = 2 * FP_TILE * sizeof(double2) + (size_t)P.ntabs * FP_NT * sizeof(uint16_t);
+    static bool attr_set = false;
+    if (!attr_set) {
+        QSV_CUDA(cudaFuncSetAttribute(k_fused_pass, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)(2 * FP_TILE * sizeof(double2) + FP_MAX_TABS * FP_NT * sizeof(uint16_t))));
+        attr_set = true;
+    }
+    unsigned grid = (unsigned)std::min<uint64_t>(P.ntiles, (uint64_t)s->num_sms);
+    k_fused_pass<<<grid, FP_NT, smem, s->stream>>>(s->amp, P);
+    QSV_CUDA(cudaGetLastError());
+    s->ctr.kernel_launches++;
+    s->ctr.state_passes++;
+    return QSV_OK;
+}
+
 static bool direct_capable(const HGate& g) {
     if (g.diag || g.k < 1 || g.k > 2) return false;
     int src[4];
@@ -1433,12 +1755,23 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
             std::vector<PassParams> params(passes.size());
             std::vector<ClPass> cparams(passes.size());
             std::vector<size_t> ops_off(passes.size()), data_off(passes.size()), subs_off(passes.size());
-            std::vector<char> kind(passes.size(), 0);  // 0 legacy tile, 1 cluster, 2 direct
+            std::vector<char> kind(passes.size(), 0);  // 0 legacy tile, 1 cluster, 2 direct, 3 fused
+            std::vector<FusedBuilt> fparams(s->use_fused && cluster && T == FP_T ? passes.size() : 0);
             std::vector<char> stage;
             for (size_t i = 0; i < passes.size(); ++i) {
                 if (s->use_direct && passes[i].gate_ids.size() == 1 && direct_capable(seg[passes[i].gate_ids[0]])) {
                     kind[i] = 2;
-                } else if (cluster) {
+                    continue;
+                }
+                if (!fparams.empty()) {
+                    bool ok = false;
+                    QSV_TRY(build_fused_pass(s, seg, passes[i], stage, fparams[i], ok));
+                    if (ok) {
+                        kind[i] = 3;
+                        continue;
+                    }
+                }
+                if (cluster) {
                     kind[i] = 1;
                     QSV_TRY(build_cluster_pass(s, seg, passes[i], T, stage, cparams[i], ops_off[i], subs_off[i],
                                                data_off[i]));
@@ -1460,6 +1793,11 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
                 char* base = (char*)s->scratch;
                 if (kind[i] == 2) {
                     QSV_TRY(launch_direct(s, seg[passes[i].gate_ids[0]]));
+                } else if (kind[i] == 3) {
+                    fparams[i].P.tabs = (const uint16_t*)(base + fparams[i].tabs_off);
+                    fparams[i].P.diags = (const FpDiag*)(base + fparams[i].diags_off);
+                    fparams[i].P.gdata = (const double2*)(base + fparams[i].gdata_off);
+                    QSV_TRY(launch_fused_pass(s, fparams[i].P));
                 } else if (kind[i] == 1) {
                     cparams[i].phases = (const ClPhase*)(base + ops_off[i]);
                     cparams[i].subs = (const ClSub*)(base + subs_off[i]);

@@ -120,6 +120,8 @@ int qsv_state_alloc(qsv_state** out, int n_qubits, int n_local, int device, cuda
     s->tile_threads = env_int("QSV_TILE_THREADS", 256);
     s->use_direct = env_int("QSV_USE_DIRECT", 1);
     s->use_cluster = env_int("QSV_USE_CLUSTER", 1);
+    s->use_fused = env_int("QSV_USE_FUSED", 1);
+    s->use_direct_store = env_int("QSV_DIRECT_STORE", 1);
     *out = s;
     return QSV_OK;
 }
@@ -162,6 +164,8 @@ extern "C" int qsv_clone(const qsv_state* s, qsv_state** out) {
     c->tile_threads = s->tile_threads;
     c->use_direct = s->use_direct;
     c->use_cluster = s->use_cluster;
+    c->use_fused = s->use_fused;
+    c->use_direct_store = s->use_direct_store;
     QSV_CUDA(cudaStreamSynchronize(s->stream));
     QSV_CUDA(cudaMemcpyAsync(c->amp, s->amp, (size_t)16 << s->n_local, cudaMemcpyDeviceToDevice,
                              c->stream));
@@ -289,6 +293,10 @@ extern "C" int qsv_set_option(qsv_state* s, const char* name, int64_t value) {
         s->use_direct = value != 0;
     } else if (!strcmp(name, "use_cluster")) {
         s->use_cluster = value != 0;
+    } else if (!strcmp(name, "use_fused")) {
+        s->use_fused = value != 0;
+    } else if (!strcmp(name, "direct_store")) {
+        s->use_direct_store = value != 0;
     } else if (!strncmp(name, "dist_", 5)) {
         return qsv_dist_set_option(s, name, value);
     } else {

@@ -124,6 +124,24 @@ def test_tile_configurations(tile_bits, low_bits, threads):
     assert np.max(np.abs(sv.data - want)) < ATOL
 
 
+@pytest.mark.parametrize("fused,direct_store", [(1, 1), (1, 0), (0, 0)])
+def test_fused_pass_paths(fused, direct_store):
+    """k_fused_pass (persistent, pipelined; with and without the direct register->global store of
+    the last phase) and k_cluster_pass must agree with the oracle on deep mixed circuits."""
+    for n, count, seed, names in [(12, 150, 1, None), (13, 200, 2, None), (17, 300, 3, None),
+                                  (16, 300, 4, ["cx", "ry", "rz", "h", "cz", "swap"]),
+                                  (15, 200, 5, ["cp", "h", "rzz", "rx", "ccx", "y", "cy"])]:
+        named = random_named_circuit(n, count, seed=seed, names=names)
+        psi = random_state(n, 11 * n + seed)
+        sv = Statevector(psi)
+        sv.set_option("use_fused", fused)
+        sv.set_option("direct_store", direct_store)
+        sv.apply_gate_list(lib.named_to_matrices(named))
+        want = ref.apply_gate_list(psi, oracle_matrices(named))
+        assert np.max(np.abs(sv.data - want)) < ATOL, (n, seed)
+        assert sv.counters()["state_passes"] < count
+
+
 @pytest.mark.parametrize("n,depth", [(20, 20), (22, 4), (24, 2)])
 def test_quantum_volume_spot_checks(n, depth):
     """configs[0] circuit in full (20 q, depth 20) and larger spot checks."""
