@@ -33,8 +33,8 @@
 enum { FP_D1C = 0, FP_D1R = 1, FP_D2C = 2, FP_D2R = 3, FP_DIAG = 4 };
 
 struct FpPhase {           // 80 bytes
-    uint16_t rd[16];       // register r is read from slot (thread slot ^ rd[r])
-    uint16_t wr[16];       // ... and written to slot (thread slot ^ wr[r])
+    uint16_t rd[16];       // register r is read from byte offset (thread offset ^ rd[r]) of the tile buffer
+    uint16_t wr[16];       // ... and written to (thread offset ^ wr[r]); slot masks pre-multiplied by 16
     uint32_t rcoef, wcoef; // 16 complex factors applied after the read / before the write (gdata offset)
     uint16_t sub_first;
     uint8_t nsub;
@@ -72,6 +72,10 @@ struct FpPass {
     const FpDiag* diags;
     const double2* gdata;  // diagonal tables and coefficient vectors
     uint64_t st_off[16];   // direct store: global offset of register r
+    uint64_t row_off[16];  // copy-in / copy-out: global offset of tile row r (256 elements per row)
+    int32_t nseg;          // tile index -> tile base: base |= ((tile >> src) & mask) << dst per segment
+    uint8_t seg_src[16], seg_dst[16];
+    uint32_t seg_mask[16];
     uint8_t st_tpos[8];    // direct store: tile bit of thread bit j
     FpPhase phases[FP_MAX_PHASES];
     FpSub subs[FP_MAX_SUBS];
@@ -223,11 +227,14 @@ __device__ __forceinline__ void fp_apply(double2 (&v)[16], const FpPass& P, int 
     }
 }
 
-// dynamic smem: [2][4096] double2 tile buffers, then [ntabs][256] u16 tables
-__global__ void __launch_bounds__(FP_NT, 1) k_fused_pass(double2* __restrict__ amp, const __grid_constant__ FpPass P) {
+// dynamic smem: [4096] double2 tile buffer, then [ntabs][256] u16 tables.  Two CTAs per SM: while
+// one waits for its tile or at a barrier the other computes; in a direct-store last phase the
+// buffer is free as soon as every thread has read its registers, so the next tile's cp.async
+// copies are issued before that phase's arithmetic.
+__global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* __restrict__ amp, const __grid_constant__ FpPass P) {
     extern __shared__ __align__(16) unsigned char fp_smem[];
-    double2* const buf0 = reinterpret_cast<double2*>(fp_smem);
-    uint16_t* const tabs_sm = reinterpret_cast<uint16_t*>(fp_smem + 2 * FP_TILE * sizeof(double2));
+    unsigned char* const tilebuf = fp_smem;
+    uint16_t* const tabs_sm = reinterpret_cast<uint16_t*>(fp_smem + FP_TILE * sizeof(double2));
     const uint32_t t = threadIdx.x;
 
     for (int i = t; i < P.ntabs * (FP_NT / 2); i += FP_NT)   // two u16 per word
@@ -237,61 +244,53 @@ __global__ void __launch_bounds__(FP_NT, 1) k_fused_pass(double2* __restrict__ a
     uint64_t cp_off = 0;
 #pragma unroll
     for (int b = 0; b < 8; ++b) cp_off |= (uint64_t)((t >> b) & 1u) << P.pos[b];
-    uint64_t row_off[16];
-#pragma unroll
-    for (int r = 0; r < 16; ++r) {
-        uint64_t o = 0;
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-            if ((r >> j) & 1) o |= 1ull << P.pos[8 + j];
-        row_off[r] = o;
-    }
-    const uint32_t st = fp_swz(t);
+    const uint32_t st16 = fp_swz(t) << 4;
     // direct-store mapping of the last phase
     uint64_t st_thread = 0;
 #pragma unroll
     for (int b = 0; b < 8; ++b) st_thread |= (uint64_t)((t >> b) & 1u) << P.pos[P.st_tpos[b]];
 
     auto tile_base_of = [&](uint32_t tile) {
-        uint64_t base = tile;
-#pragma unroll
-        for (int b = 0; b < FP_T; ++b) base = insert_zero(base, P.pos[b]);
+        uint64_t base = 0;
+        for (int sgm = 0; sgm < P.nseg; ++sgm)
+            base |= (uint64_t)((tile >> P.seg_src[sgm]) & P.seg_mask[sgm]) << P.seg_dst[sgm];
         return base;
     };
-    auto issue_load = [&](uint32_t tile, double2* buf) {
-        const double2* __restrict__ g = amp + tile_base_of(tile) + cp_off;
+    auto issue_load = [&](uint64_t tile_base) {
+        const double2* __restrict__ g = amp + tile_base + cp_off;
+        const uint32_t dst0 = (uint32_t)__cvta_generic_to_shared(tilebuf);
 #pragma unroll
         for (int r = 0; r < 16; ++r) {
-            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(buf + (st ^ fp_swz((uint32_t)r << 8)));
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(g + row_off[r]));
+            const uint32_t dst = dst0 + (st16 ^ (fp_swz((uint32_t)r << 8) << 4));
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(g + P.row_off[r]));
         }
         asm volatile("cp.async.commit_group;\n" ::: "memory");
     };
 
     uint32_t tile = blockIdx.x;
-    if (tile < P.ntiles) issue_load(tile, buf0);
-    int cur = 0;
-    __syncthreads();  // tables visible
-    for (; tile < P.ntiles; tile += gridDim.x, cur ^= 1) {
-        double2* const tilebuf = buf0 + cur * FP_TILE;
+    if (tile >= P.ntiles) return;
+    uint64_t tile_base = tile_base_of(tile);
+    issue_load(tile_base);
+    while (true) {
+        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+        __syncthreads();  // tile (and, first time, the tables) visible to every thread
         const uint32_t next = tile + gridDim.x;
-        if (next < P.ntiles) {
-            issue_load(next, buf0 + (cur ^ 1) * FP_TILE);
-            asm volatile("cp.async.wait_group 1;\n" ::: "memory");
-        } else {
-            asm volatile("cp.async.wait_group 0;\n" ::: "memory");
-        }
-        __syncthreads();
-        const uint64_t tile_base = tile_base_of(tile);
+        const bool has_next = next < P.ntiles;
+        const uint64_t next_base = has_next ? tile_base_of(next) : 0;
         const uint64_t diag_base = tile_base | P.index_base;
         bool stored = false;
 #pragma unroll 1
         for (int p = 0; p < P.nphases; ++p) {
             const FpPhase& ph = P.phases[p];
-            const uint32_t sb = tabs_sm[ph.tab * FP_NT + t];
+            const uint32_t sb = (uint32_t)tabs_sm[ph.tab * FP_NT + t] << 4;
             double2 v[16];
 #pragma unroll
-            for (int r = 0; r < 16; ++r) v[r] = tilebuf[sb ^ ph.rd[r]];
+            for (int r = 0; r < 16; ++r) v[r] = *reinterpret_cast<const double2*>(tilebuf + (sb ^ ph.rd[r]));
+            if (ph.direct) {
+                // every thread has its registers: the buffer can take the next tile now
+                __syncthreads();
+                if (has_next) issue_load(next_base);
+            }
             if (ph.rcoef != FP_NOCOEF) {
                 const double2* __restrict__ c = P.gdata + ph.rcoef;
 #pragma unroll
@@ -312,15 +311,20 @@ __global__ void __launch_bounds__(FP_NT, 1) k_fused_pass(double2* __restrict__ a
                 stored = true;
             } else {
 #pragma unroll
-                for (int r = 0; r < 16; ++r) tilebuf[sb ^ ph.wr[r]] = v[r];
+                for (int r = 0; r < 16; ++r) *reinterpret_cast<double2*>(tilebuf + (sb ^ ph.wr[r])) = v[r];
+                __syncthreads();
             }
-            __syncthreads();
         }
         if (!stored) {
             double2* __restrict__ g = amp + tile_base + cp_off;
 #pragma unroll
-            for (int r = 0; r < 16; ++r) g[row_off[r]] = tilebuf[st ^ fp_swz((uint32_t)r << 8)];
+            for (int r = 0; r < 16; ++r)
+                g[P.row_off[r]] = *reinterpret_cast<const double2*>(tilebuf + (st16 ^ (fp_swz((uint32_t)r << 8) << 4)));
             __syncthreads();
+            if (has_next) issue_load(next_base);
         }
+        if (!has_next) break;
+        tile = next;
+        tile_base = next_base;
     }
 }

@@ -1519,7 +1519,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
             uint32_t m = 0;
             for (int j = 0; j < 4; ++j)
                 if ((nib >> j) & 1) m ^= fp_swz(1u << rpos[j]);
-            return (uint16_t)m;
+            return (uint16_t)(m << 4);
         };
         // compose the leading / trailing permutations into one map of the 16 register slots
         auto compose = [&](int which, int* src16, cplx* c16) {
@@ -1665,6 +1665,28 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
         }
         ph.nsub = (uint8_t)cnt;
     }
+    for (int r = 0; r < 16; ++r) {
+        uint64_t o = 0;
+        for (int j = 0; j < 4; ++j)
+            if ((r >> j) & 1) o |= 1ull << P.pos[8 + j];
+        P.row_off[r] = o;
+    }
+    // runs of consecutive non-tile index bits: tile number bits [src, src+len) land at [dst, dst+len)
+    P.nseg = 0;
+    for (int b = 0, src = 0; b < n;) {
+        if ((active >> b) & 1ull) {
+            ++b;
+            continue;
+        }
+        int e = b;
+        while (e < n && !((active >> e) & 1ull)) ++e;
+        P.seg_src[P.nseg] = (uint8_t)src;
+        P.seg_dst[P.nseg] = (uint8_t)b;
+        P.seg_mask[P.nseg] = (e - b) >= 32 ? 0xffffffffu : ((1u << (e - b)) - 1u);
+        ++P.nseg;
+        src += e - b;
+        b = e;
+    }
     P.nphases = (int)sels.size();
     P.ntabs = (int)(tabs.size() / FP_NT);
     P.ntiles = (uint32_t)(1ull << (n - FP_T));
@@ -1685,14 +1707,14 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
 }
 
 static int launch_fused_pass(qsv_state* s, const FpPass& P) {
-    const size_t smem = 2 * FP_TILE * sizeof(double2) + (size_t)P.ntabs * FP_NT * sizeof(uint16_t);
+    const size_t smem = FP_TILE * sizeof(double2) + (size_t)P.ntabs * FP_NT * sizeof(uint16_t);
     static bool attr_set = false;
     if (!attr_set) {
         QSV_CUDA(cudaFuncSetAttribute(k_fused_pass, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)(2 * FP_TILE * sizeof(double2) + FP_MAX_TABS * FP_NT * sizeof(uint16_t))));
+                                      (int)(FP_TILE * sizeof(double2) + FP_MAX_TABS * FP_NT * sizeof(uint16_t))));
         attr_set = true;
     }
-    unsigned grid = (unsigned)std::min<uint64_t>(P.ntiles, (uint64_t)s->num_sms);
+    unsigned grid = (unsigned)std::min<uint64_t>(P.ntiles, (uint64_t)s->num_sms * 2);
     k_fused_pass<<<grid, FP_NT, smem, s->stream>>>(s->amp, P);
     QSV_CUDA(cudaGetLastError());
     s->ctr.kernel_launches++;
