@@ -156,6 +156,9 @@ int qsv_timer_end(qsv_state* s, float* ms_out);
 int qsv_set_option(qsv_state* s, const char* name, int64_t value);
 /* write a buffer larger than L2 (flush between timed iterations) */
 int qsv_flush_l2(qsv_state* s);
+/* Host-only view of the single-GPU pass planner (no device work, usable without a GPU): one
+ * line per planned pass (kernel kind, tile bits, phases, op counts) is written to `path`. */
+int qsv_debug_plan(int n_qubits, const qsv_gate* gates, uint64_t n_gates, int flags, const char* path);
 
 /* ---- sharded states (one process per GPU; NCCL over NVLink) -------------- */
 /* 128-byte ncclUniqueId for the bootstrap; rank 0 creates it and the host side

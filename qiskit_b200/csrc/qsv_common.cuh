@@ -66,6 +66,7 @@ struct qsv_state {
     int use_cluster; // fused passes through k_cluster_pass (register phases) instead of k_tile_pass
     int use_fused;   // fused passes through k_fused_pass (persistent, pipelined) when the tile is 2^12
     int use_direct_store;  // k_fused_pass: last phase stores registers straight to global memory
+    int use_warp_local;    // k_fused_pass: warp-private sub-tiles when three tile bits stay untouched
     int num_sms;
     qsv_counters ctr;
     // sharding

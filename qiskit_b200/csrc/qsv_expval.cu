@@ -433,6 +433,7 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
             aux->use_cluster = s->use_cluster;
             aux->use_fused = s->use_fused;
             aux->use_direct_store = s->use_direct_store;
+            aux->use_warp_local = s->use_warp_local;
             s->aux = aux;
         } else if (rc == QSV_ERR_NOMEM) {
             for (QwcGroup* g : rotated) direct.insert(direct.end(), g->members.begin(), g->members.end());

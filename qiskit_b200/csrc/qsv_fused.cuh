@@ -67,12 +67,13 @@ struct FpPass {
     uint32_t ntiles;
     int32_t nphases;
     int32_t ntabs;
+    int32_t warp_local;    // phases exchange data inside warps only (__syncwarp between phases)
     int32_t pos[FP_T];     // ascending global bit position of tile bit b
     const uint16_t* tabs;  // [ntabs][256]
     const FpDiag* diags;
     const double2* gdata;  // diagonal tables and coefficient vectors
-    uint64_t st_off[16];   // direct store: global offset of register r
-    uint64_t row_off[16];  // copy-in / copy-out: global offset of tile row r (256 elements per row)
+    uint64_t st_off[16];   // direct store: global BYTE offset of register r
+    uint64_t row_off[16];  // copy-in / copy-out: global BYTE offset of tile row r (256 elements per row)
     int32_t nseg;          // tile index -> tile base: base |= ((tile >> src) & mask) << dst per segment
     uint8_t seg_src[16], seg_dst[16];
     uint32_t seg_mask[16];
@@ -181,6 +182,13 @@ __device__ __forceinline__ void fp_d2r(double2 (&v)[16], const FpPass& P, int mo
     }
 }
 
+// v *= c without a register copy: the two products by c.y go to temporaries, the FMAs land in place
+__device__ __forceinline__ void fp_cmul_inplace(double2& v, const double2 c) {
+    const double t = c.y * v.y, u = c.y * v.x;
+    v.x = fma(c.x, v.x, -t);
+    v.y = fma(c.x, v.y, u);
+}
+
 __device__ __forceinline__ void fp_diag(double2 (&v)[16], const FpPass& P, int di, const uint16_t* __restrict__ tabs_sm,
                                         uint64_t tile_base) {
     const FpDiag* __restrict__ d = P.diags + di;
@@ -192,10 +200,10 @@ __device__ __forceinline__ void fp_diag(double2 (&v)[16], const FpPass& P, int d
     if ((w0.y >> 24) & 1u) {
         const double2 c = __ldg(tab);
 #pragma unroll
-        for (int r = 0; r < 16; ++r) v[r] = cmul(v[r], c);
+        for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], c);
     } else {
 #pragma unroll
-        for (int r = 0; r < 16; ++r) v[r] = cmul(v[r], __ldg(tab + d->regpart[r]));
+        for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], __ldg(tab + d->regpart[r]));
     }
 }
 
@@ -257,7 +265,7 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* __restrict__ a
         return base;
     };
     auto issue_load = [&](uint64_t tile_base) {
-        const double2* __restrict__ g = amp + tile_base + cp_off;
+        const char* __restrict__ g = reinterpret_cast<const char*>(amp + tile_base + cp_off);
         const uint32_t dst0 = (uint32_t)__cvta_generic_to_shared(tilebuf);
 #pragma unroll
         for (int r = 0; r < 16; ++r) {
@@ -294,7 +302,7 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* __restrict__ a
             if (ph.rcoef != FP_NOCOEF) {
                 const double2* __restrict__ c = P.gdata + ph.rcoef;
 #pragma unroll
-                for (int r = 0; r < 16; ++r) v[r] = cmul(__ldg(c + r), v[r]);
+                for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], __ldg(c + r));
             }
             const int s0 = ph.sub_first, s1 = s0 + ph.nsub;
 #pragma unroll 1
@@ -302,24 +310,26 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* __restrict__ a
             if (ph.wcoef != FP_NOCOEF) {
                 const double2* __restrict__ c = P.gdata + ph.wcoef;
 #pragma unroll
-                for (int r = 0; r < 16; ++r) v[r] = cmul(__ldg(c + r), v[r]);
+                for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], __ldg(c + r));
             }
             if (ph.direct) {
-                double2* __restrict__ g = amp + tile_base + st_thread;
+                char* __restrict__ g = reinterpret_cast<char*>(amp + tile_base + st_thread);
 #pragma unroll
-                for (int r = 0; r < 16; ++r) g[P.st_off[r]] = v[r];
+                for (int r = 0; r < 16; ++r) *reinterpret_cast<double2*>(g + P.st_off[r]) = v[r];
                 stored = true;
             } else {
 #pragma unroll
                 for (int r = 0; r < 16; ++r) *reinterpret_cast<double2*>(tilebuf + (sb ^ ph.wr[r])) = v[r];
-                __syncthreads();
+                if (P.warp_local && p + 1 < P.nphases) __syncwarp();
+                else __syncthreads();
             }
         }
         if (!stored) {
-            double2* __restrict__ g = amp + tile_base + cp_off;
+            char* __restrict__ g = reinterpret_cast<char*>(amp + tile_base + cp_off);
 #pragma unroll
             for (int r = 0; r < 16; ++r)
-                g[P.row_off[r]] = *reinterpret_cast<const double2*>(tilebuf + (st16 ^ (fp_swz((uint32_t)r << 8) << 4)));
+                *reinterpret_cast<double2*>(g + P.row_off[r]) =
+                    *reinterpret_cast<const double2*>(tilebuf + (st16 ^ (fp_swz((uint32_t)r << 8) << 4)));
             __syncthreads();
             if (has_next) issue_load(next_base);
         }

@@ -687,7 +687,13 @@ static double gate_cost(const HGate& g) {
     const int dim = 1 << g.k;
     if (g.diag) return 1.0;
     int src[1 << 3];
-    if (g.k <= 3 && mat_is_mono(g.m, dim, src)) return 1.0;
+    if (g.k <= 3 && mat_is_mono(g.m, dim, src)) {
+        // a pure permutation is folded into addressing (free); one with phases costs a complex
+        // multiply per amplitude, more than the shared phase table a diagonal gate joins
+        bool unit = true;
+        for (int r = 0; r < dim; ++r) unit &= (g.m[(size_t)r * dim + src[r]] == cplx(1.0, 0.0));
+        return unit ? 0.25 : 1.5;
+    }
     double c = 4.0 * dim;  // DFMA per amplitude of a dense complex block
     if (mat_is_real(g.m)) c *= 0.5;
     return c;
@@ -1468,11 +1474,27 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
                 done[i] = 1;
                 ++ndone;
             }
-            for (int b = FP_T - 1; b >= 0 && __builtin_popcount(ps.S) < 4; --b) ps.S |= 1u << b;
             sels.push_back(std::move(ps));
         }
     }
     if (sels.empty() || sels.size() > FP_MAX_PHASES) return QSV_OK;
+    // Warp-local passes: three tile bits that no dense / permutation op of the pass touches become
+    // the warp index in EVERY phase.  A warp then owns the same 512 amplitudes from the first
+    // phase to the last and phases only need __syncwarp().
+    uint32_t W = 0;
+    {
+        uint32_t touched = 0;
+        for (const PhaseSel& ps : sels) touched |= ps.S;
+        const uint32_t untouched = ((1u << FP_T) - 1u) & ~touched;
+        if (s->use_warp_local && __builtin_popcount(untouched) >= 3) {
+            for (int b = FP_T - 1; b >= 0 && __builtin_popcount(W) < 3; --b)
+                if ((untouched >> b) & 1u) W |= 1u << b;
+        }
+        for (PhaseSel& ps : sels)
+            for (int b = FP_T - 1; b >= 0 && __builtin_popcount(ps.S) < 4; --b)
+                if (!((W >> b) & 1u)) ps.S |= 1u << b;
+    }
+    P.warp_local = W ? 1 : 0;
 
     std::vector<uint16_t> tabs;
     std::vector<FpDiag> diags;
@@ -1491,7 +1513,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
         const bool direct = (pi + 1 == sels.size()) && low4 && !(S & 15u) && s->use_direct_store;
         // thread bits
         int tpos[8], nt = 0;
-        uint32_t rest = ((1u << FP_T) - 1u) & ~S;
+        uint32_t rest = ((1u << FP_T) - 1u) & ~S & ~W;
         if (!direct) {
             // lanes 0..2 on three tile bits with distinct (bit mod 3): a quarter-warp's 16-byte
             // accesses then fall into distinct swizzled columns
@@ -1505,6 +1527,8 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
         }
         for (int b = 0; b < FP_T; ++b)
             if ((rest >> b) & 1u) tpos[nt++] = b;
+        for (int b = 0; b < FP_T; ++b)
+            if ((W >> b) & 1u) tpos[nt++] = b;  // thread bits 5..7 = warp index
         if (nt != 8) QSV_FAIL(QSV_ERR_UNSUPPORTED, "internal: fused pass thread bits");
         uint16_t base_of[FP_NT];
         for (int t = 0; t < FP_NT; ++t) {
@@ -1586,7 +1610,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
                 uint64_t off = 0;
                 for (int j = 0; j < 4; ++j)
                     if ((dst16[q] >> j) & 1) off |= 1ull << P.pos[rpos[j]];
-                P.st_off[q] = off;
+                P.st_off[q] = off * sizeof(double2);
             }
         }
         ph.sub_first = (uint16_t)nsubs;
@@ -1669,7 +1693,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
         uint64_t o = 0;
         for (int j = 0; j < 4; ++j)
             if ((r >> j) & 1) o |= 1ull << P.pos[8 + j];
-        P.row_off[r] = o;
+        P.row_off[r] = o * sizeof(double2);
     }
     // runs of consecutive non-tile index bits: tile number bits [src, src+len) land at [dst, dst+len)
     P.nseg = 0;
@@ -1706,6 +1730,19 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
     return QSV_OK;
 }
 
+static void trace_fused_pass(const FpPass& P, FILE* f) {
+    int cnt[5] = {0, 0, 0, 0, 0};
+    fprintf(f, "[fused] T bits:");
+    for (int b = 0; b < FP_T; ++b) fprintf(f, " %d", P.pos[b]);
+    fprintf(f, " | %sphases %d:", P.warp_local ? "warp-local " : "", P.nphases);
+    for (int p = 0; p < P.nphases; ++p) {
+        fprintf(f, " [%d%s%s%s]", P.phases[p].nsub, P.phases[p].direct ? "d" : "",
+                P.phases[p].rcoef != FP_NOCOEF ? "r" : "", P.phases[p].wcoef != FP_NOCOEF ? "w" : "");
+        for (int i = 0; i < P.phases[p].nsub; ++i) cnt[P.subs[P.phases[p].sub_first + i].kind]++;
+    }
+    fprintf(f, " | d1c %d d1r %d d2c %d d2r %d diag %d | tabs %d\n", cnt[0], cnt[1], cnt[2], cnt[3], cnt[4], P.ntabs);
+}
+
 static int launch_fused_pass(qsv_state* s, const FpPass& P) {
     const size_t smem = FP_TILE * sizeof(double2) + (size_t)P.ntabs * FP_NT * sizeof(uint16_t);
     static bool attr_set = false;
@@ -1714,9 +1751,19 @@ static int launch_fused_pass(qsv_state* s, const FpPass& P) {
                                       (int)(FP_TILE * sizeof(double2) + FP_MAX_TABS * FP_NT * sizeof(uint16_t))));
         attr_set = true;
     }
+    static const bool trace = getenv("QSV_TRACE") != nullptr;
+    if (trace) trace_fused_pass(P, stderr);
     unsigned grid = (unsigned)std::min<uint64_t>(P.ntiles, (uint64_t)s->num_sms * 2);
+    if (trace) QSV_CUDA(cudaEventRecord(s->ev0, s->stream));
     k_fused_pass<<<grid, FP_NT, smem, s->stream>>>(s->amp, P);
     QSV_CUDA(cudaGetLastError());
+    if (trace) {
+        float ms = 0.f;
+        QSV_CUDA(cudaEventRecord(s->ev1, s->stream));
+        QSV_CUDA(cudaEventSynchronize(s->ev1));
+        QSV_CUDA(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+        fprintf(stderr, "        -> %.3f ms\n", ms);
+    }
     s->ctr.kernel_launches++;
     s->ctr.state_passes++;
     return QSV_OK;
@@ -1761,6 +1808,8 @@ static bool tile_capable(const HGate& g) {
 }
 
 // Apply classified gates whose qubits are all local (physical bits < n_local).
+static thread_local FILE* g_plan_dump = nullptr;
+
 int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
     const bool no_fusion = flags & QSV_FLAG_NO_FUSION;
     if (!no_fusion) fuse_gates(gates, s->n_local);
@@ -1800,6 +1849,19 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
                 } else {
                     QSV_TRY(build_pass(s, seg, passes[i], T, stage, params[i], ops_off[i], data_off[i]));
                 }
+            }
+            if (g_plan_dump) {  // host-only planning (qsv_debug_plan): report and skip the device work
+                for (size_t i = 0; i < passes.size(); ++i) {
+                    fprintf(g_plan_dump, "pass kind=%d gates=%zu ", (int)kind[i], passes[i].gate_ids.size());
+                    if (kind[i] == 3) trace_fused_pass(fparams[i].P, g_plan_dump);
+                    else fprintf(g_plan_dump, "\n");
+                }
+                if (end < gates.size()) {
+                    fprintf(g_plan_dump, "pass kind=big k=%d\n", gates[end].k);
+                    ++end;
+                }
+                start = end;
+                continue;
             }
             const size_t used = stage.size();
             if (used) {
@@ -1857,9 +1919,16 @@ static int validate_qargs(const qsv_state* s, int k, const int* qargs, const cha
 // sharded states: make every qubit the stream needs local (qsv_dist.cu)
 int qsv_dist_apply(qsv_state* s, std::vector<HGate>& gates, int flags);
 
+static int qsv_apply_gates_impl(qsv_state* s, const qsv_gate* gates, uint64_t n_gates, int flags);
+void qsv_state_defaults(qsv_state* s);  // qsv_state.cu
+
 extern "C" int qsv_apply_gates(qsv_state* s, const qsv_gate* gates, uint64_t n_gates, int flags) {
     if (!s || (!gates && n_gates)) QSV_FAIL(QSV_ERR_INVALID, "qsv_apply_gates: NULL argument");
     QSV_CUDA(cudaSetDevice(s->device));
+    return qsv_apply_gates_impl(s, gates, n_gates, flags);
+}
+
+static int qsv_apply_gates_impl(qsv_state* s, const qsv_gate* gates, uint64_t n_gates, int flags) {
     std::vector<HGate> hg;
     hg.reserve(n_gates);
     cplx gphase(1.0, 0.0);
@@ -1902,6 +1971,30 @@ extern "C" int qsv_apply_gates(qsv_state* s, const qsv_gate* gates, uint64_t n_g
     if (hg.empty()) return QSV_OK;
     if (s->world > 1) return qsv_dist_apply(s, hg, flags);
     return qsv_apply_hgates(s, hg, flags);
+}
+
+// Host-only view of the single-GPU pass planner (no device work): writes one line per pass to
+// `path`.  Used to study fusion offline; not part of the simulation path.
+extern "C" int qsv_debug_plan(int n_qubits, const qsv_gate* gates, uint64_t n_gates, int flags, const char* path) {
+    if (n_qubits < 1 || n_qubits > 40 || !path) QSV_FAIL(QSV_ERR_INVALID, "qsv_debug_plan: bad argument");
+    FILE* f = fopen(path, "w");
+    if (!f) QSV_FAIL(QSV_ERR_INVALID, "qsv_debug_plan: cannot open %s", path);
+    qsv_state st;
+    memset(&st, 0, sizeof st);
+    st.n = st.n_local = n_qubits;
+    st.world = 1;
+    st.num_sms = 148;
+    for (int q = 0; q < 64; ++q) st.perm[q] = q;
+    qsv_state_defaults(&st);
+    g_plan_dump = f;
+    cudaSetDevice(0);  // may fail without a device: irrelevant here
+    cudaGetLastError();
+    int rc = qsv_apply_gates_impl(&st, gates, n_gates, flags);
+    g_plan_dump = nullptr;
+    fprintf(f, "counters: passes=%llu phases=%llu\n", (unsigned long long)st.ctr.state_passes,
+            (unsigned long long)st.ctr.phases);
+    fclose(f);
+    return rc;
 }
 
 extern "C" int qsv_apply_matrix(qsv_state* s, const double* mat, int k, const int* qargs) {

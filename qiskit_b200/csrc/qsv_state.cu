@@ -69,6 +69,17 @@ static int env_int(const char* name, int dflt) {
     return v && *v ? atoi(v) : dflt;
 }
 
+void qsv_state_defaults(qsv_state* s) {
+    s->tile_bits = env_int("QSV_TILE_BITS", 12);
+    s->low_bits = env_int("QSV_LOW_BITS", 4);
+    s->tile_threads = env_int("QSV_TILE_THREADS", 256);
+    s->use_direct = env_int("QSV_USE_DIRECT", 1);
+    s->use_cluster = env_int("QSV_USE_CLUSTER", 1);
+    s->use_fused = env_int("QSV_USE_FUSED", 1);
+    s->use_direct_store = env_int("QSV_DIRECT_STORE", 1);
+    s->use_warp_local = env_int("QSV_WARP_LOCAL", 0);  // measured: no gain (barriers are not the limiter), and its 32-byte store segments cost 20 %
+}
+
 int qsv_state_alloc(qsv_state** out, int n_qubits, int n_local, int device, cudaStream_t share_stream) {
     if (!out) QSV_FAIL(QSV_ERR_INVALID, "qsv_create: out is NULL");
     *out = nullptr;
@@ -115,13 +126,7 @@ int qsv_state_alloc(qsv_state** out, int n_qubits, int n_local, int device, cuda
     cudaDeviceProp prop;
     QSV_CUDA(cudaGetDeviceProperties(&prop, device));
     s->num_sms = prop.multiProcessorCount;
-    s->tile_bits = env_int("QSV_TILE_BITS", 12);
-    s->low_bits = env_int("QSV_LOW_BITS", 4);
-    s->tile_threads = env_int("QSV_TILE_THREADS", 256);
-    s->use_direct = env_int("QSV_USE_DIRECT", 1);
-    s->use_cluster = env_int("QSV_USE_CLUSTER", 1);
-    s->use_fused = env_int("QSV_USE_FUSED", 1);
-    s->use_direct_store = env_int("QSV_DIRECT_STORE", 1);
+    qsv_state_defaults(s);
     *out = s;
     return QSV_OK;
 }
@@ -166,6 +171,7 @@ extern "C" int qsv_clone(const qsv_state* s, qsv_state** out) {
     c->use_cluster = s->use_cluster;
     c->use_fused = s->use_fused;
     c->use_direct_store = s->use_direct_store;
+    c->use_warp_local = s->use_warp_local;
     QSV_CUDA(cudaStreamSynchronize(s->stream));
     QSV_CUDA(cudaMemcpyAsync(c->amp, s->amp, (size_t)16 << s->n_local, cudaMemcpyDeviceToDevice,
                              c->stream));
@@ -297,6 +303,8 @@ extern "C" int qsv_set_option(qsv_state* s, const char* name, int64_t value) {
         s->use_fused = value != 0;
     } else if (!strcmp(name, "direct_store")) {
         s->use_direct_store = value != 0;
+    } else if (!strcmp(name, "warp_local")) {
+        s->use_warp_local = value != 0;
     } else if (!strncmp(name, "dist_", 5)) {
         return qsv_dist_set_option(s, name, value);
     } else {
