@@ -74,6 +74,7 @@ typedef struct qsv_counters {
     uint64_t phases;          /* register-cluster phases executed inside fused passes */
     uint64_t swap_count;      /* sharded states: global<->local qubit exchanges */
     uint64_t swap_bytes;      /* bytes this rank sent over NVLink in those exchanges */
+    uint64_t write_passes;    /* write-only sweeps (basis / product-state initialisation) */
 } qsv_counters;
 
 /* ---- library ---------------------------------------------------------- */

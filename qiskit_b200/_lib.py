@@ -45,6 +45,7 @@ class QsvCounters(C.Structure):
         ("phases", C.c_uint64),
         ("swap_count", C.c_uint64),
         ("swap_bytes", C.c_uint64),
+        ("write_passes", C.c_uint64),
     ]
 
 

@@ -78,6 +78,13 @@ struct qsv_state {
     // shares this handle's stream; owned by this handle)
     qsv_state* aux;
     int owns_stream;
+    // lazy |index>: qsv_init_basis only records the index; the buffer is written by the first entry
+    // point that needs amplitudes (qsv_materialize) or, better, by the product-state prologue of
+    // qsv_apply_gates, which then never has to read the zeros
+    int basis_pending;
+    int lazy_init;  // option: 0 = qsv_init_basis writes the buffer immediately
+    int use_product_init;  // option: product-state prologue in qsv_apply_gates
+    uint64_t basis_index;
 };
 
 int qsv_state_alloc(qsv_state** out, int n_qubits, int n_local, int device, cudaStream_t share_stream);
@@ -95,6 +102,7 @@ struct HGate {
 // apply gates whose qubits are all local physical bits (qsv_gate.cu)
 int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags);
 
+int qsv_materialize(qsv_state* s);  // write a pending |index> into the amplitude buffer
 int qsv_ensure_scratch(qsv_state* s, size_t bytes);
 int qsv_ensure_pinned(qsv_state* s, size_t bytes);
 

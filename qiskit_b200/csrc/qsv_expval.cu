@@ -337,6 +337,7 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
         QSV_FAIL(QSV_ERR_INVALID, "qsv_expval_pauli_batch: NULL argument");
     if (n_terms == 0) return QSV_OK;
     QSV_CUDA(cudaSetDevice(s->device));
+    QSV_TRY(qsv_materialize(s));
     const uint64_t full = s->n >= 64 ? ~0ull : ((1ull << s->n) - 1);
     std::vector<TermItem> items(n_terms);
     for (uint64_t t = 0; t < n_terms; ++t) {
@@ -434,6 +435,7 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
             aux->use_fused = s->use_fused;
             aux->use_direct_store = s->use_direct_store;
             aux->use_warp_local = s->use_warp_local;
+            aux->lazy_init = 0;
             s->aux = aux;
         } else if (rc == QSV_ERR_NOMEM) {
             for (QwcGroup* g : rotated) direct.insert(direct.end(), g->members.begin(), g->members.end());
@@ -596,6 +598,7 @@ extern "C" int qsv_norm2(const qsv_state* cs, double* out) {
     qsv_state* s = const_cast<qsv_state*>(cs);
     if (!s || !out) QSV_FAIL(QSV_ERR_INVALID, "qsv_norm2: NULL argument");
     QSV_CUDA(cudaSetDevice(s->device));
+    QSV_TRY(qsv_materialize(s));
     double r[2];
     QSV_TRY(inner_impl(s, s->amp, s->amp, r));
     *out = r[0];
@@ -611,6 +614,8 @@ extern "C" int qsv_inner(const qsv_state* ca, const qsv_state* cb, double* out_c
     for (int q = 0; q < a->n; ++q)
         if (a->perm[q] != b->perm[q]) QSV_FAIL(QSV_ERR_UNSUPPORTED, "qsv_inner: states have different qubit layouts");
     QSV_CUDA(cudaSetDevice(a->device));
+    QSV_TRY(qsv_materialize(a));
+    QSV_TRY(qsv_materialize(b));
     QSV_CUDA(cudaStreamSynchronize(b->stream));
     return inner_impl(a, a->amp, b->amp, out_c128);
 }

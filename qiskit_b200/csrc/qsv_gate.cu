@@ -1922,6 +1922,92 @@ int qsv_dist_apply(qsv_state* s, std::vector<HGate>& gates, int flags);
 static int qsv_apply_gates_impl(qsv_state* s, const qsv_gate* gates, uint64_t n_gates, int flags);
 void qsv_state_defaults(qsv_state* s);  // qsv_state.cu
 
+// amp[i] = lo[i mod 2^h] * hi[i div 2^h]: a product state from two half-register tables
+__global__ void __launch_bounds__(256) k_product_state(double2* __restrict__ amp, uint64_t count, int h,
+                                                       const double2* __restrict__ lo,
+                                                       const double2* __restrict__ hi) {
+    const uint64_t stride = (uint64_t)gridDim.x * 256;
+    const uint64_t mask = (1ull << h) - 1;
+    for (uint64_t i = blockIdx.x * 256ull + threadIdx.x; i < count; i += stride)
+        amp[i] = cmul(__ldg(lo + (i & mask)), __ldg(hi + (i >> h)));
+}
+
+// Product-state prologue (single GPU, state = pending |index>): every one-qubit gate that comes
+// before the first multi-qubit gate on its qubit acts on a product state, so it is applied to
+// that qubit's 2-vector on the host; the state is then written once as the tensor product.
+// Consumed gates are removed from `hg`.  Does nothing (basis stays pending) if no gate qualifies.
+static int product_prologue(qsv_state* s, std::vector<HGate>& hg) {
+    const int n = s->n_local;
+    cplx vec[64][2];
+    for (int q = 0; q < n; ++q) {
+        const int bit = (int)((s->basis_index >> q) & 1ull);
+        vec[q][0] = bit ? 0.0 : 1.0;
+        vec[q][1] = bit ? 1.0 : 0.0;
+    }
+    const uint64_t all = n >= 64 ? ~0ull : ((1ull << n) - 1);
+    uint64_t blocked = 0;
+    std::vector<char> consumed(hg.size(), 0);
+    size_t count = 0;
+    for (size_t i = 0; i < hg.size() && blocked != all; ++i) {
+        const HGate& g = hg[i];
+        uint64_t m = 0;
+        for (int j = 0; j < g.k; ++j) m |= 1ull << g.q[j];
+        if (g.k == 1 && !(m & blocked)) {
+            cplx* v = vec[g.q[0]];
+            if (g.diag) {
+                v[0] *= g.m[0];
+                v[1] *= g.m[1];
+            } else {
+                const cplx a = g.m[0] * v[0] + g.m[1] * v[1], b = g.m[2] * v[0] + g.m[3] * v[1];
+                v[0] = a;
+                v[1] = b;
+            }
+            consumed[i] = 1;
+            ++count;
+        } else {
+            blocked |= m;
+        }
+    }
+    if (!count) return QSV_OK;
+    const int h = (n + 1) / 2;
+    const size_t nlo = (size_t)1 << h, nhi = (size_t)1 << (n - h);
+    const size_t bytes = (nlo + nhi) * sizeof(double2);
+    QSV_TRY(qsv_ensure_scratch(s, bytes + 256));
+    QSV_TRY(qsv_ensure_pinned(s, bytes + 256));
+    QSV_CUDA(cudaStreamSynchronize(s->stream));  // pinned staging reuse
+    cplx* tab = reinterpret_cast<cplx*>(s->pinned);
+    auto fill = [&](cplx* t, int q0, int nq) {  // t[i] = prod_j vec[q0 + j][bit j of i]
+        t[0] = 1.0;
+        for (int j = 0; j < nq; ++j) {
+            const size_t half = (size_t)1 << j;
+            for (size_t i = 0; i < half; ++i) {
+                t[i + half] = t[i] * vec[q0 + j][1];
+                t[i] = t[i] * vec[q0 + j][0];
+            }
+        }
+    };
+    fill(tab, 0, h);
+    fill(tab + nlo, h, n - h);
+    QSV_CUDA(cudaMemcpyAsync(s->scratch, s->pinned, bytes, cudaMemcpyHostToDevice, s->stream));
+    s->ctr.h2d_bytes += bytes;
+    const uint64_t total = qsv_local_size(s);
+    uint64_t blocks = (total + 255) / 256;
+    const uint64_t cap = (uint64_t)s->num_sms * 16;
+    if (blocks > cap) blocks = cap;
+    const double2* d_lo = reinterpret_cast<const double2*>(s->scratch);
+    k_product_state<<<(unsigned)blocks, 256, 0, s->stream>>>(s->amp, total, h, d_lo, d_lo + nlo);
+    QSV_CUDA(cudaGetLastError());
+    s->ctr.kernel_launches++;
+    s->ctr.write_passes++;
+    s->basis_pending = 0;
+    std::vector<HGate> rest;
+    rest.reserve(hg.size() - count);
+    for (size_t i = 0; i < hg.size(); ++i)
+        if (!consumed[i]) rest.push_back(std::move(hg[i]));
+    hg.swap(rest);
+    return QSV_OK;
+}
+
 extern "C" int qsv_apply_gates(qsv_state* s, const qsv_gate* gates, uint64_t n_gates, int flags) {
     if (!s || (!gates && n_gates)) QSV_FAIL(QSV_ERR_INVALID, "qsv_apply_gates: NULL argument");
     QSV_CUDA(cudaSetDevice(s->device));
@@ -1967,6 +2053,12 @@ static int qsv_apply_gates_impl(qsv_state* s, const qsv_gate* gates, uint64_t n_
     if (gphase != cplx(1.0, 0.0)) {
         if (hg.empty()) return qsv_scale(s, gphase.real(), gphase.imag());
         for (cplx& v : hg[0].m) v *= gphase;
+    }
+    if (s->basis_pending && !g_plan_dump) {
+        // |index> is still only recorded: fold the leading one-qubit gates into a product state and
+        // write it in one sweep (no zero fill, no read); otherwise write |index> now
+        if (!(flags & QSV_FLAG_NO_FUSION) && s->use_product_init) QSV_TRY(product_prologue(s, hg));
+        QSV_TRY(qsv_materialize(s));
     }
     if (hg.empty()) return QSV_OK;
     if (s->world > 1) return qsv_dist_apply(s, hg, flags);

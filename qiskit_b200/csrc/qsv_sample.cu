@@ -322,6 +322,7 @@ extern "C" int qsv_probabilities(const qsv_state* cs, const int* qargs, int m, d
     if (!s || !host_out) QSV_FAIL(QSV_ERR_INVALID, "qsv_probabilities: NULL argument");
     if (!qargs) m = s->n;
     QSV_CUDA(cudaSetDevice(s->device));
+    QSV_TRY(qsv_materialize(const_cast<qsv_state*>(s)));
     if (s->world > 1) QSV_FAIL(QSV_ERR_UNSUPPORTED, "qsv_probabilities: sharded states (use qsv_sample / expval)");
     GatherBits G;
     bool identity;
@@ -351,6 +352,7 @@ extern "C" int qsv_sample(const qsv_state* cs, const int* qargs, int m, const do
     if (!s || (shots && (!uniforms || !out_indices))) QSV_FAIL(QSV_ERR_INVALID, "qsv_sample: NULL argument");
     if (!qargs) m = s->n;
     QSV_CUDA(cudaSetDevice(s->device));
+    QSV_TRY(qsv_materialize(const_cast<qsv_state*>(s)));
     if (s->world > 1) {
         if (m != s->n) QSV_FAIL(QSV_ERR_UNSUPPORTED, "qsv_sample: sharded states sample all qubits only");
         for (int j = 0; j < m; ++j)
@@ -465,6 +467,7 @@ extern "C" int qsv_collapse(qsv_state* s, const int* qargs, int m, uint64_t outc
                             int rotate_to_zero) {
     if (!s || (!qargs && m)) QSV_FAIL(QSV_ERR_INVALID, "qsv_collapse: NULL argument");
     QSV_CUDA(cudaSetDevice(s->device));
+    QSV_TRY(qsv_materialize(const_cast<qsv_state*>(s)));
     if (s->world > 1) QSV_FAIL(QSV_ERR_UNSUPPORTED, "qsv_collapse: sharded states");
     GatherBits G;
     bool identity;

@@ -77,6 +77,8 @@ void qsv_state_defaults(qsv_state* s) {
     s->use_cluster = env_int("QSV_USE_CLUSTER", 1);
     s->use_fused = env_int("QSV_USE_FUSED", 1);
     s->use_direct_store = env_int("QSV_DIRECT_STORE", 1);
+    s->lazy_init = env_int("QSV_LAZY_INIT", 1);
+    s->use_product_init = env_int("QSV_PRODUCT_INIT", 1);
     s->use_warp_local = env_int("QSV_WARP_LOCAL", 0);  // measured: no gain (barriers are not the limiter), and its 32-byte store segments cost 20 %
 }
 
@@ -172,6 +174,10 @@ extern "C" int qsv_clone(const qsv_state* s, qsv_state** out) {
     c->use_fused = s->use_fused;
     c->use_direct_store = s->use_direct_store;
     c->use_warp_local = s->use_warp_local;
+    c->lazy_init = s->lazy_init;
+    c->use_product_init = s->use_product_init;
+    QSV_TRY(qsv_materialize(const_cast<qsv_state*>(s)));
+    c->basis_pending = 0;
     QSV_CUDA(cudaStreamSynchronize(s->stream));
     QSV_CUDA(cudaMemcpyAsync(c->amp, s->amp, (size_t)16 << s->n_local, cudaMemcpyDeviceToDevice,
                              c->stream));
@@ -185,6 +191,8 @@ extern "C" int qsv_copy_state(qsv_state* dst, const qsv_state* src) {
         dst->world != src->world)
         QSV_FAIL(QSV_ERR_INVALID, "qsv_copy_state: handles differ in size, device or sharding");
     QSV_CUDA(cudaSetDevice(src->device));
+    QSV_TRY(qsv_materialize(const_cast<qsv_state*>(src)));
+    dst->basis_pending = 0;
     QSV_CUDA(cudaStreamSynchronize(src->stream));
     QSV_CUDA(cudaMemcpyAsync(dst->amp, src->amp, (size_t)16 << src->n_local, cudaMemcpyDeviceToDevice,
                              dst->stream));
@@ -201,22 +209,39 @@ extern "C" int qsv_num_qubits(const qsv_state* s, int* out) {
 
 __global__ void k_set_one(double2* amp, uint64_t idx) { amp[idx] = make_double2(1.0, 0.0); }
 
-extern "C" int qsv_init_basis(qsv_state* s, uint64_t index) {
-    if (!s) QSV_FAIL(QSV_ERR_INVALID, "qsv_init_basis: state is NULL");
-    if (s->n < 64 && index >> s->n)
-        QSV_FAIL(QSV_ERR_INVALID, "qsv_init_basis: index %llu out of range for %d qubits",
-                 (unsigned long long)index, s->n);
-    QSV_CUDA(cudaSetDevice(s->device));
+static int write_basis(qsv_state* s, uint64_t index) {
     QSV_CUDA(cudaMemsetAsync(s->amp, 0, (size_t)16 << s->n_local, s->stream));
-    for (int q = 0; q < 64; ++q) s->perm[q] = q;
     uint64_t owner = s->world > 1 ? index >> s->n_local : 0;
     if ((int)owner == s->rank) {
         uint64_t local = index & (qsv_local_size(s) - 1);
         k_set_one<<<1, 1, 0, s->stream>>>(s->amp, local);
         s->ctr.kernel_launches++;
     }
+    s->ctr.write_passes++;
     QSV_CUDA(cudaGetLastError());
     return QSV_OK;
+}
+
+int qsv_materialize(qsv_state* s) {
+    if (!s->basis_pending) return QSV_OK;
+    s->basis_pending = 0;
+    return write_basis(s, s->basis_index);
+}
+
+extern "C" int qsv_init_basis(qsv_state* s, uint64_t index) {
+    if (!s) QSV_FAIL(QSV_ERR_INVALID, "qsv_init_basis: state is NULL");
+    if (s->n < 64 && index >> s->n)
+        QSV_FAIL(QSV_ERR_INVALID, "qsv_init_basis: index %llu out of range for %d qubits",
+                 (unsigned long long)index, s->n);
+    QSV_CUDA(cudaSetDevice(s->device));
+    for (int q = 0; q < 64; ++q) s->perm[q] = q;
+    if (s->world == 1 && s->lazy_init) {  // deferred: see qsv_state::basis_pending
+        s->basis_pending = 1;
+        s->basis_index = index;
+        return QSV_OK;
+    }
+    s->basis_pending = 0;
+    return write_basis(s, index);
 }
 
 int qsv_dist_canonicalize(qsv_state* s);  // qsv_dist.cu: restore the identity qubit layout
@@ -228,6 +253,8 @@ extern "C" int qsv_upload(qsv_state* s, const double* c128, uint64_t offset, uin
                  (unsigned long long)offset, (unsigned long long)(offset + count),
                  (unsigned long long)qsv_local_size(s));
     QSV_CUDA(cudaSetDevice(s->device));
+    if (count == qsv_local_size(s)) s->basis_pending = 0;  // a full overwrite needs no zeros first
+    QSV_TRY(qsv_materialize(s));
     if (s->world > 1) QSV_TRY(qsv_dist_canonicalize(s));
     QSV_CUDA(cudaMemcpyAsync(s->amp + offset, c128, count * 16, cudaMemcpyHostToDevice, s->stream));
     QSV_CUDA(cudaStreamSynchronize(s->stream));
@@ -241,6 +268,7 @@ extern "C" int qsv_download(const qsv_state* cs, double* c128, uint64_t offset, 
     if (offset + count > qsv_local_size(s))
         QSV_FAIL(QSV_ERR_INVALID, "qsv_download: range exceeds the local slab");
     QSV_CUDA(cudaSetDevice(s->device));
+    QSV_TRY(qsv_materialize(s));
     if (s->world > 1) QSV_TRY(qsv_dist_canonicalize(s));
     QSV_CUDA(cudaMemcpyAsync(c128, s->amp + offset, count * 16, cudaMemcpyDeviceToHost, s->stream));
     QSV_CUDA(cudaStreamSynchronize(s->stream));
@@ -305,6 +333,11 @@ extern "C" int qsv_set_option(qsv_state* s, const char* name, int64_t value) {
         s->use_direct_store = value != 0;
     } else if (!strcmp(name, "warp_local")) {
         s->use_warp_local = value != 0;
+    } else if (!strcmp(name, "product_init")) {
+        s->use_product_init = value != 0;
+    } else if (!strcmp(name, "lazy_init")) {
+        QSV_TRY(qsv_materialize(s));
+        s->lazy_init = value != 0;
     } else if (!strncmp(name, "dist_", 5)) {
         return qsv_dist_set_option(s, name, value);
     } else {
@@ -341,6 +374,7 @@ __global__ void k_scale(double2* amp, uint64_t n, double2 c) {
 extern "C" int qsv_scale(qsv_state* s, double re, double im) {
     if (!s) QSV_FAIL(QSV_ERR_INVALID, "qsv_scale: state is NULL");
     QSV_CUDA(cudaSetDevice(s->device));
+    QSV_TRY(qsv_materialize(s));
     uint64_t n = qsv_local_size(s);
     uint64_t blocks = (n + 255) / 256;
     uint64_t cap = (uint64_t)s->num_sms * 16;

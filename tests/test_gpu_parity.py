@@ -142,6 +142,35 @@ def test_fused_pass_paths(fused, direct_store):
         assert sv.counters()["state_passes"] < count
 
 
+@pytest.mark.parametrize("n", [1, 2, 5, 12, 13, 17])
+def test_product_state_prologue_and_lazy_basis(n):
+    """qsv_init_basis is lazy and qsv_apply_gates folds the leading one-qubit gates of every qubit
+    into a product state written in one sweep: same amplitudes as gate-by-gate application."""
+    rng = np.random.default_rng(n)
+    names = ["ry", "rz", "h", "rx", "u", "x", "s"] + (["cx", "cz", "rzz"] if n > 1 else [])
+    for start in (0, (1 << n) - 1, int(rng.integers(1 << n))):
+        named = random_named_circuit(n, 8 * n + 5, seed=n + start, names=names)
+        gates = lib.named_to_matrices(named)
+        want = ref.apply_gate_list(ref.basis_state(n, start), oracle_matrices(named))
+        for product_init in (1, 0):
+            sv = Statevector.from_int(start, 1 << n)
+            sv.set_option("product_init", product_init)
+            w0 = sv.counters()["write_passes"]      # pooled handles keep cumulative counters
+            sv.apply_gate_list(gates)
+            assert np.max(np.abs(sv.data - want)) < ATOL, (n, start, product_init)
+            assert sv.counters()["write_passes"] == w0 + 1
+    # every reader materialises a pending |index>
+    sv = Statevector.from_int(3 % (1 << n), 1 << n)
+    assert abs(sv._norm2() - 1) < 1e-15 and sv.data[3 % (1 << n)] == 1
+    sv = Statevector.from_int(0, 1 << n)
+    assert sv.probabilities()[0] == 1.0
+    sv = Statevector.from_int(0, 1 << n)
+    cp = sv.copy()
+    assert cp.data[0] == 1 and sv.data[0] == 1
+    sv = Statevector.from_int(0, 1 << n)
+    assert (sv * 2j).data[0] == 2j
+
+
 @pytest.mark.parametrize("n,depth", [(20, 20), (22, 4), (24, 2)])
 def test_quantum_volume_spot_checks(n, depth):
     """configs[0] circuit in full (20 q, depth 20) and larger spot checks."""
