@@ -81,6 +81,8 @@ struct qsv_state {
     // lazy |index>: qsv_init_basis only records the index; the buffer is written by the first entry
     // point that needs amplitudes (qsv_materialize) or, better, by the product-state prologue of
     // qsv_apply_gates, which then never has to read the zeros
+    // out-of-place request: the next pass reads its tiles from this buffer instead of `amp`
+    const double2* read_from;
     int basis_pending;
     int lazy_init;  // option: 0 = qsv_init_basis writes the buffer immediately
     int use_product_init;  // option: product-state prologue in qsv_apply_gates

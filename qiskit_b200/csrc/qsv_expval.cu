@@ -452,9 +452,8 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
         const double r2 = 0.70710678118654752440;
         for (QwcGroup* g : rotated) {
             if (!have_copy) {
-                QSV_CUDA(cudaMemcpyAsync(aux->amp, s->amp, (size_t)16 << s->n_local,
-                                         cudaMemcpyDeviceToDevice, s->stream));
-                s->ctr.state_passes++;
+                // no copy: the first rotation pass reads the state and writes the scratch buffer
+                aux->read_from = s->amp;
                 have_copy = true;
                 cur_x = cur_z = 0;
             }
@@ -484,6 +483,12 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
                 layer.push_back(hg);
                 cur_x = (cur_x & ~b) | ((want ? b : 0));
                 cur_z = (cur_z & ~b) | ((want == 2 ? b : 0));
+            }
+            if (layer.empty() && aux->read_from) {
+                QSV_CUDA(cudaMemcpyAsync(aux->amp, s->amp, (size_t)16 << s->n_local, cudaMemcpyDeviceToDevice,
+                                         s->stream));
+                s->ctr.state_passes++;
+                aux->read_from = nullptr;
             }
             if (!layer.empty()) {
                 const uint64_t before_l = aux->ctr.kernel_launches, before_p = aux->ctr.state_passes;

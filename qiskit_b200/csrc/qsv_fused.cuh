@@ -239,7 +239,9 @@ __device__ __forceinline__ void fp_apply(double2 (&v)[16], const FpPass& P, int 
 // one waits for its tile or at a barrier the other computes; in a direct-store last phase the
 // buffer is free as soon as every thread has read its registers, so the next tile's cp.async
 // copies are issued before that phase's arithmetic.
-__global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* __restrict__ amp, const __grid_constant__ FpPass P) {
+// `src` = `amp` for the usual in-place pass; a different `src` makes the pass out of place (tiles are
+// read from src and written to amp), which saves the scratch copy of basis-change expectation values.
+__global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const double2* src, const __grid_constant__ FpPass P) {
     extern __shared__ __align__(16) unsigned char fp_smem[];
     unsigned char* const tilebuf = fp_smem;
     uint16_t* const tabs_sm = reinterpret_cast<uint16_t*>(fp_smem + FP_TILE * sizeof(double2));
@@ -265,7 +267,7 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* __restrict__ a
         return base;
     };
     auto issue_load = [&](uint64_t tile_base) {
-        const char* __restrict__ g = reinterpret_cast<const char*>(amp + tile_base + cp_off);
+        const char* g = reinterpret_cast<const char*>(src + tile_base + cp_off);
         const uint32_t dst0 = (uint32_t)__cvta_generic_to_shared(tilebuf);
 #pragma unroll
         for (int r = 0; r < 16; ++r) {
@@ -313,7 +315,7 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* __restrict__ a
                 for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], __ldg(c + r));
             }
             if (ph.direct) {
-                char* __restrict__ g = reinterpret_cast<char*>(amp + tile_base + st_thread);
+                char* g = reinterpret_cast<char*>(amp + tile_base + st_thread);
 #pragma unroll
                 for (int r = 0; r < 16; ++r) *reinterpret_cast<double2*>(g + P.st_off[r]) = v[r];
                 stored = true;
@@ -325,7 +327,7 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* __restrict__ a
             }
         }
         if (!stored) {
-            char* __restrict__ g = reinterpret_cast<char*>(amp + tile_base + cp_off);
+            char* g = reinterpret_cast<char*>(amp + tile_base + cp_off);
 #pragma unroll
             for (int r = 0; r < 16; ++r)
                 *reinterpret_cast<double2*>(g + P.row_off[r]) =

@@ -1755,7 +1755,9 @@ static int launch_fused_pass(qsv_state* s, const FpPass& P) {
     if (trace) trace_fused_pass(P, stderr);
     unsigned grid = (unsigned)std::min<uint64_t>(P.ntiles, (uint64_t)s->num_sms * 2);
     if (trace) QSV_CUDA(cudaEventRecord(s->ev0, s->stream));
-    k_fused_pass<<<grid, FP_NT, smem, s->stream>>>(s->amp, P);
+    const double2* src = s->read_from ? s->read_from : s->amp;
+    s->read_from = nullptr;  // only the first pass after the request reads the other buffer
+    k_fused_pass<<<grid, FP_NT, smem, s->stream>>>(s->amp, src, P);
     QSV_CUDA(cudaGetLastError());
     if (trace) {
         float ms = 0.f;
@@ -1873,6 +1875,12 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
                 QSV_CUDA(cudaMemcpyAsync(s->scratch, s->pinned, used, cudaMemcpyHostToDevice, s->stream));
                 s->ctr.h2d_bytes += used;
             }
+            if (s->read_from && kind[0] != 3) {  // out-of-place request, but the first pass cannot do it
+                QSV_CUDA(cudaMemcpyAsync(s->amp, s->read_from, (size_t)16 << s->n_local, cudaMemcpyDeviceToDevice,
+                                         s->stream));
+                s->ctr.state_passes++;
+                s->read_from = nullptr;
+            }
             for (size_t i = 0; i < passes.size(); ++i) {
                 char* base = (char*)s->scratch;
                 if (kind[i] == 2) {
@@ -1895,6 +1903,12 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
             }
         }
         if (end < gates.size()) {
+            if (s->read_from) {
+                QSV_CUDA(cudaMemcpyAsync(s->amp, s->read_from, (size_t)16 << s->n_local, cudaMemcpyDeviceToDevice,
+                                         s->stream));
+                s->ctr.state_passes++;
+                s->read_from = nullptr;
+            }
             QSV_TRY(apply_dense_big(s, gates[end]));
             ++end;
         }
