@@ -254,6 +254,16 @@ def measured_peak():
     return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
 
 
+def ncu_traffic(kernel: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed
+    `ncu --set full` summary (profiles/ncu_traffic.json; a bench run is never made under ncu)."""
+    path = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if not os.path.exists(path):
+        return None
+    entry = json.load(open(path)).get(kernel)
+    return None if entry is None else entry["bytes_per_launch"]
+
+
 def roofline_gate_stream(args, device) -> dict:
     """Unfusable stream: one dense 2-qubit gate per pass at `roofline_qubits` qubits."""
     from qiskit_b200 import Statevector, _lib
@@ -299,9 +309,9 @@ def roofline_gate_stream(args, device) -> dict:
     norm = sv._norm2()
     peak, peak_src = measured_peak()
     return {
-        "bound": "hbm", "kernel": "k_tile_pass (one dense 2-qubit gate per pass)",
+        "bound": "hbm", "kernel": "k_direct2<false> (one dense 2-qubit gate per launch, register resident)",
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "peak_source": peak_src, "traffic": None,
+        "peak_source": peak_src, "traffic": ncu_traffic("k_direct2"),
         "algorithmic_bytes_per_launch": bytes_per_pass,
         "avg_launch_ms": ms.value / max(passes, 1),
         "_detail": {
