@@ -369,8 +369,13 @@ static int dist_swap_bits(qsv_state* s, int k, const int* gpos, const int* lpos)
         A.peer[j] = d->peer_amp[r];
     }
     const int npeers = (1 << k) - 1;
-    cudaEvent_t e0 = s->ev0;  // not used for timing here; transport time is measured by callers
-    (void)e0;
+    static const bool trace = getenv("QSV_TRACE") != nullptr;
+    cudaEvent_t te0 = nullptr, te1 = nullptr;
+    if (trace) {
+        QSV_CUDA(cudaEventCreate(&te0));
+        QSV_CUDA(cudaEventCreate(&te1));
+        QSV_CUDA(cudaEventRecord(te0, s->stream));
+    }
     if (d->use_p2p) {
         QSV_TRY(dist_barrier(s));
         uint64_t blocks = ((A.rest >> 1) + 256 * 4 - 1) / (256 * 4);
@@ -415,6 +420,18 @@ static int dist_swap_bits(qsv_state* s, int k, const int* gpos, const int* lpos)
             QSV_CUDA(cudaGetLastError());
             s->ctr.kernel_launches += 2;
         }
+    }
+    if (trace) {
+        float ms = 0.f;
+        QSV_CUDA(cudaEventRecord(te1, s->stream));
+        QSV_CUDA(cudaEventSynchronize(te1));
+        QSV_CUDA(cudaEventElapsedTime(&ms, te0, te1));
+        cudaEventDestroy(te0);
+        cudaEventDestroy(te1);
+        const double gb = (double)npeers * A.rest * 16 / 1e9;
+        if (s->rank == 0)
+            fprintf(stderr, "[swap] k=%d %s sent %.2f GB/rank in %.3f ms = %.1f GB/s per direction\n", k,
+                    d->use_p2p ? "p2p" : "nccl", gb, ms, gb / (ms / 1e3));
     }
     s->ctr.swap_count++;
     s->ctr.swap_bytes += (uint64_t)npeers * A.rest * 16;
