@@ -27,7 +27,8 @@
 #define FP_MAX_PHASES 12
 #define FP_MAX_SUBS 112
 #define FP_MAX_MAT 1408  // doubles of matrix data per pass
-#define FP_MAX_TABS 40   // per-thread u16 tables (one per phase + one per diagonal op)
+#define FP_MAX_TABS 48   // per-thread u16 tables (one per phase + one per diagonal op)
+#define FP_MAX_DIAGS 40  // diagonal ops per pass
 #define FP_NOCOEF 0xffffffffu
 
 enum { FP_D1C = 0, FP_D1R = 1, FP_D2C = 2, FP_D2R = 3, FP_DIAG = 4 };
@@ -50,7 +51,7 @@ struct FpSub {             // 8 bytes
     uint32_t pad;
 };
 
-struct FpDiag {            // 64 bytes, global memory
+struct FpDiag {            // 64 bytes, kernel parameter (uniform: the off-tile bits are gathered once per warp)
     uint32_t table_off;    // into gdata (double2 units)
     uint16_t tab;          // per-thread table: table index bits contributed by the thread
     uint8_t nglob;         // table index bits fed by index bits outside the tile
@@ -70,7 +71,6 @@ struct FpPass {
     int32_t warp_local;    // phases exchange data inside warps only (__syncwarp between phases)
     int32_t pos[FP_T];     // ascending global bit position of tile bit b
     const uint16_t* tabs;  // [ntabs][256]
-    const FpDiag* diags;
     const double2* gdata;  // diagonal tables and coefficient vectors
     uint64_t st_off[16];   // direct store: global BYTE offset of register r
     uint64_t row_off[16];  // copy-in / copy-out: global BYTE offset of tile row r (256 elements per row)
@@ -81,6 +81,7 @@ struct FpPass {
     FpPhase phases[FP_MAX_PHASES];
     FpSub subs[FP_MAX_SUBS];
     double mats[FP_MAX_MAT];
+    FpDiag diags[FP_MAX_DIAGS];
 };
 
 __host__ __device__ __forceinline__ uint32_t fp_swz(uint32_t i) {
@@ -191,19 +192,18 @@ __device__ __forceinline__ void fp_cmul_inplace(double2& v, const double2 c) {
 
 __device__ __forceinline__ void fp_diag(double2 (&v)[16], const FpPass& P, int di, const uint16_t* __restrict__ tabs_sm,
                                         uint64_t tile_base) {
-    const FpDiag* __restrict__ d = P.diags + di;
-    const uint4 w0 = __ldg(reinterpret_cast<const uint4*>(d));  // table_off, tab|nglob|all_same, regpart[0..3]
-    uint32_t thr = tabs_sm[(w0.y & 0xffffu) * FP_NT + threadIdx.x];
-    const int nglob = (w0.y >> 16) & 255;
-    for (int j = 0; j < nglob; ++j) thr |= (uint32_t)((tile_base >> d->gbit[j]) & 1ull) << d->gj[j];
-    const double2* __restrict__ tab = P.gdata + w0.x + thr;
-    if ((w0.y >> 24) & 1u) {
+    const FpDiag& d = P.diags[di];
+    uint32_t glob = 0;  // uniform: table index bits fed by index bits outside the tile
+    for (int j = 0; j < d.nglob; ++j) glob |= (uint32_t)((tile_base >> d.gbit[j]) & 1ull) << d.gj[j];
+    const uint32_t thr = tabs_sm[d.tab * FP_NT + threadIdx.x] | glob;
+    const double2* __restrict__ tab = P.gdata + d.table_off + thr;
+    if (d.all_same) {
         const double2 c = __ldg(tab);
 #pragma unroll
         for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], c);
     } else {
 #pragma unroll
-        for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], __ldg(tab + d->regpart[r]));
+        for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], __ldg(tab + d.regpart[r]));
     }
 }
 

@@ -1622,7 +1622,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
             FpSub& sb = P.subs[nsubs];
             memset(&sb, 0, sizeof sb);
             if (op.kind == CL_DIAG) {
-                if (tabs.size() / FP_NT >= FP_MAX_TABS || diags.size() >= 65535) return QSV_OK;
+                if (tabs.size() / FP_NT >= FP_MAX_TABS || diags.size() >= FP_MAX_DIAGS) return QSV_OK;
                 FpDiag d;
                 memset(&d, 0, sizeof d);
                 d.table_off = (uint32_t)gdata.size();
@@ -1720,10 +1720,10 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
     const size_t gdata_bytes = gdata.size() * sizeof(double2);
     out.tabs_off = (stage.size() + 63) & ~(size_t)63;
     out.diags_off = (out.tabs_off + tabs_bytes + 63) & ~(size_t)63;
-    out.gdata_off = (out.diags_off + diag_bytes + 63) & ~(size_t)63;
+    out.gdata_off = (out.diags_off + 63) & ~(size_t)63;
     stage.resize(out.gdata_off + gdata_bytes);
     memcpy(stage.data() + out.tabs_off, tabs.data(), tabs_bytes);
-    if (diag_bytes) memcpy(stage.data() + out.diags_off, diags.data(), diag_bytes);
+    if (diag_bytes) memcpy(P.diags, diags.data(), diag_bytes);
     if (gdata_bytes) memcpy(stage.data() + out.gdata_off, gdata.data(), gdata_bytes);
     s->ctr.phases += sels.size();
     ok = true;
@@ -1887,7 +1887,6 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
                     QSV_TRY(launch_direct(s, seg[passes[i].gate_ids[0]]));
                 } else if (kind[i] == 3) {
                     fparams[i].P.tabs = (const uint16_t*)(base + fparams[i].tabs_off);
-                    fparams[i].P.diags = (const FpDiag*)(base + fparams[i].diags_off);
                     fparams[i].P.gdata = (const double2*)(base + fparams[i].gdata_off);
                     QSV_TRY(launch_fused_pass(s, fparams[i].P));
                 } else if (kind[i] == 1) {
