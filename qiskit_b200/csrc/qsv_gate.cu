@@ -1753,11 +1753,24 @@ static int launch_fused_pass(qsv_state* s, const FpPass& P) {
     }
     static const bool trace = getenv("QSV_TRACE") != nullptr;
     if (trace) trace_fused_pass(P, stderr);
-    unsigned grid = (unsigned)std::min<uint64_t>(P.ntiles, (uint64_t)s->num_sms * 2);
     if (trace) QSV_CUDA(cudaEventRecord(s->ev0, s->stream));
     const double2* src = s->read_from ? s->read_from : s->amp;
     s->read_from = nullptr;  // only the first pass after the request reads the other buffer
-    k_fused_pass<<<grid, FP_NT, smem, s->stream>>>(s->amp, src, P);
+    if (s->use_fused3) {
+        static bool attr3_set = false;
+        const size_t tabs_max = FP_MAX_TABS * FP_NT * sizeof(uint16_t);
+        if (!attr3_set) {
+            QSV_CUDA(cudaFuncSetAttribute(k_fused_pass3, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)(3 * FP_TILE * sizeof(double2) + tabs_max + 64)));
+            attr3_set = true;
+        }
+        const size_t smem3 = 3 * FP_TILE * sizeof(double2) + (size_t)P.ntabs * FP_NT * sizeof(uint16_t) + 64;
+        unsigned grid = (unsigned)std::min<uint64_t>((P.ntiles + 1) / 2, (uint64_t)s->num_sms);
+        k_fused_pass3<<<grid, FP3_NT, smem3, s->stream>>>(s->amp, src, P);
+    } else {
+        unsigned grid = (unsigned)std::min<uint64_t>(P.ntiles, (uint64_t)s->num_sms * 2);
+        k_fused_pass<<<grid, FP_NT, smem, s->stream>>>(s->amp, src, P);
+    }
     QSV_CUDA(cudaGetLastError());
     if (trace) {
         float ms = 0.f;

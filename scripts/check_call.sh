@@ -1,0 +1,6 @@
+# Round check: GPU parity tests, smoke, both bench arms, launch list of the bench.
+O=gpurun_out/${1:-chk}; mkdir -p $O
+timeout 1500 python -m pytest tests -m gpu -x -q > $O/tests.log 2>&1; echo "tests exit $?" | tee -a $O/tests.log; tail -3 $O/tests.log
+timeout 300 python __graft_entry__.py smoke > $O/smoke.log 2>&1; tail -2 $O/smoke.log
+timeout 900 python bench.py > $O/bench.json 2> $O/bench.err; echo "bench exit $?"; cat $O/bench.json
+timeout 900 python bench.py --impl reference > $O/bench_ref.json 2> $O/bench_ref.err; echo "ref exit $?"; cat $O/bench_ref.json
