@@ -78,6 +78,8 @@ struct FpPass {
     uint8_t seg_src[16], seg_dst[16];
     uint32_t seg_mask[16];
     uint8_t st_tpos[8];    // direct store: tile bit of thread bit j
+    uint16_t out_tab;      // copy-out: per-thread slot table (0xffff: slot = fp_swz(t), the copy-in layout)
+    uint16_t out_row[16];  // copy-out: slot mask of tile row r (pre-multiplied by 16)
     FpPhase phases[FP_MAX_PHASES];
     FpSub subs[FP_MAX_SUBS];
     double mats[FP_MAX_MAT];
@@ -327,11 +329,12 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const dou
             }
         }
         if (!stored) {
+            const uint32_t so16 = P.out_tab == 0xffff ? st16 : ((uint32_t)tabs_sm[P.out_tab * FP_NT + t] << 4);
             char* g = reinterpret_cast<char*>(amp + tile_base + cp_off);
 #pragma unroll
             for (int r = 0; r < 16; ++r)
                 *reinterpret_cast<double2*>(g + P.row_off[r]) =
-                    *reinterpret_cast<const double2*>(tilebuf + (st16 ^ (fp_swz((uint32_t)r << 8) << 4)));
+                    *reinterpret_cast<const double2*>(tilebuf + (so16 ^ P.out_row[r]));
             __syncthreads();
             if (has_next) issue_load(next_base);
         }
@@ -478,11 +481,12 @@ __global__ void __launch_bounds__(FP3_NT, 1) k_fused_pass3(double2* amp, const d
             }
         }
         if (!stored) {
+            const uint32_t so16 = P.out_tab == 0xffff ? st16 : ((uint32_t)tabs_sm[P.out_tab * FP_NT + t] << 4);
             char* gp = reinterpret_cast<char*>(amp + tile_base + cp_off);
 #pragma unroll
             for (int r = 0; r < 16; ++r)
                 *reinterpret_cast<double2*>(gp + P.row_off[r]) =
-                    *reinterpret_cast<const double2*>(tilebuf + (st16 ^ (fp_swz((uint32_t)r << 8) << 4)));
+                    *reinterpret_cast<const double2*>(tilebuf + (so16 ^ P.out_row[r]));
             fp3_bar(g);
             if (has_next) {
                 if (nxt != FP3_NONE) release(cur);

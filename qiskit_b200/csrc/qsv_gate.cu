@@ -1414,11 +1414,31 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
     std::vector<TileOp> ops;
     QSV_TRY(make_tile_ops(gates, plan, local_of, ops));
 
+    // Permutation gates whose index map is affine over GF(2) and whose coefficients are all 1 (X, CX,
+    // SWAP and products of them) never need register bits: the tile stays where it is in shared
+    // memory and the map "tile index -> slot" (`A`, affine) absorbs them.  Because the swizzle is
+    // XOR-linear too, slot = table[thread] ^ mask[register] keeps its form, so the kernel is unchanged.
+    std::vector<char> lin(ops.size(), 0);
+    if (s->use_linear_perm)
+        for (size_t i = 0; i < ops.size(); ++i) {
+            const TileOp& op = ops[i];
+            if (op.kind != CL_MONO || !op.unit || op.k > 3) continue;
+            bool ok_lin = true;
+            const int dim = 1 << op.k;
+            for (int x = 0; x < dim && ok_lin; ++x)
+                for (int y = 0; y < dim; ++y)
+                    if ((op.src[x ^ y] ^ op.src[0]) != ((op.src[x] ^ op.src[0]) ^ (op.src[y] ^ op.src[0]))) {
+                        ok_lin = false;
+                        break;
+                    }
+            lin[i] = ok_lin;
+        }
     // ---- phase selection: [leading permutations][dense / diagonal][trailing permutations]
     struct PhaseSel {
         uint32_t S;
         std::vector<int> sel;
-        std::vector<char> role;  // 0 mid, 1 leading permutation, 2 trailing permutation
+        std::vector<char> role;  // 0 mid, 1 leading permutation, 2 trailing permutation (both in register bits),
+                                 // 3 leading / 4 trailing affine permutation absorbed by the slot map
     };
     std::vector<PhaseSel> sels;
     {
@@ -1428,6 +1448,8 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
             PhaseSel ps;
             ps.S = 0;
             uint32_t blocked = 0;
+            uint32_t reg_lead = 0;    // bits touched by a leading permutation held in register bits
+            uint32_t free_trail = 0;  // bits touched by a trailing permutation absorbed by the slot map
             int state[FP_T];  // per tile bit: 0 untouched, 1 dense/diag seen, 2 closed by a trailing permutation
             for (int b = 0; b < FP_T; ++b) state[b] = 0;
             for (size_t i = 0; i < ops.size(); ++i) {
@@ -1453,14 +1475,25 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
                     }
                     for (int b = 0; b < FP_T; ++b)
                         if (((m >> b) & 1u) && state[b] == 0) state[b] = 1;
+                } else if (lin[i] && !(fresh && (m & reg_lead))) {
+                    // order on shared bits: slot map first, register permutations after it (read side);
+                    // register permutations first, slot map after them (write side)
+                    role = fresh ? 3 : 4;
+                    if (role == 4) {
+                        free_trail |= m;
+                        for (int b = 0; b < FP_T; ++b)
+                            if ((m >> b) & 1u) state[b] = 2;
+                    }
                 } else {
-                    if (__builtin_popcount(ps.S | m) > 4 || (ops[i].kind != CL_MONO && closed)) {
+                    if (__builtin_popcount(ps.S | m) > 4 || (ops[i].kind != CL_MONO && closed) ||
+                        (ops[i].kind == CL_MONO && !fresh && (m & free_trail))) {
                         blocked |= m;
                         continue;
                     }
                     ps.S |= m;
                     if (ops[i].kind == CL_MONO) {
                         role = fresh ? 1 : 2;
+                        if (role == 1) reg_lead |= m;
                         if (role == 2)
                             for (int b = 0; b < FP_T; ++b)
                                 if ((m >> b) & 1u) state[b] = 2;
@@ -1503,6 +1536,40 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
     bool low4 = true;  // tile bits 0..3 are index bits 0..3 (contiguous 256-byte runs)
     for (int b = 0; b < 4; ++b) low4 &= (P.pos[b] == b);
 
+    // slot map: tile index x (as the circuit sees it at this point of the pass) lives in slot
+    // fp_swz(A(x)), A(x) = off ^ XOR of col[b] over the set bits of x; identity after the copy-in
+    struct Aff {
+        uint32_t col[FP_T], off;
+        uint32_t operator()(uint32_t x) const {
+            uint32_t y = off;
+            for (int b = 0; b < FP_T; ++b)
+                if ((x >> b) & 1u) y ^= col[b];
+            return y;
+        }
+    } A;
+    A.off = 0;
+    for (int b = 0; b < FP_T; ++b) A.col[b] = 1u << b;
+    // after permutation `op` (new[x] = old[sub(x)], sub replaces the op's bits by src[...]) : A <- A o sub
+    auto absorb = [&](const TileOp& op) {
+        auto sub = [&](uint32_t x) {
+            int rr = 0;
+            for (int j = 0; j < op.k; ++j) rr |= (int)((x >> op.bits[j]) & 1u) << j;
+            uint32_t y = x;
+            for (int j = 0; j < op.k; ++j)
+                y = (y & ~(1u << op.bits[j])) | ((uint32_t)((op.src[rr] >> j) & 1) << op.bits[j]);
+            return y;
+        };
+        Aff B;
+        B.off = A(sub(0));
+        for (int b = 0; b < FP_T; ++b) B.col[b] = A(sub(1u << b)) ^ B.off;
+        A = B;
+    };
+    auto is_identity = [&]() {
+        bool id = A.off == 0;
+        for (int b = 0; b < FP_T; ++b) id &= A.col[b] == (1u << b);
+        return id;
+    };
+
     for (size_t pi = 0; pi < sels.size(); ++pi) {
         const PhaseSel& ps = sels[pi];
         const uint32_t S = ps.S;
@@ -1510,20 +1577,37 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
         int rpos[4];
         for (int b = 0, j = 0; b < FP_T; ++b)
             if ((S >> b) & 1u) rpos[j++] = b;
-        const bool direct = (pi + 1 == sels.size()) && low4 && !(S & 15u) && s->use_direct_store;
+        bool has_trail = false;
+        for (size_t i = 0; i < ps.sel.size(); ++i) {
+            if (ps.role[i] == 3) absorb(ops[ps.sel[i]]);
+            has_trail |= ps.role[i] == 4;
+        }
+        const bool direct = (pi + 1 == sels.size()) && low4 && !(S & 15u) && s->use_direct_store && !has_trail;
         // thread bits
         int tpos[8], nt = 0;
         uint32_t rest = ((1u << FP_T) - 1u) & ~S & ~W;
         if (!direct) {
-            // lanes 0..2 on three tile bits with distinct (bit mod 3): a quarter-warp's 16-byte
-            // accesses then fall into distinct swizzled columns
-            for (int c = 0; c < 3; ++c)
-                for (int b = 0; b < FP_T; ++b)
-                    if (((rest >> b) & 1u) && b % 3 == c) {
-                        tpos[nt++] = b;
-                        rest &= ~(1u << b);
-                        break;
+            // lanes 0..2 on three tile bits whose slots differ in linearly independent swizzled
+            // columns (slot bits 0..2): a quarter-warp's 16-byte accesses are then conflict free.
+            // With the identity slot map these are three bits with distinct (bit mod 3).
+            auto colv = [&](int b) { return fp_swz(A.col[b]) & 7u; };
+            bool found = false;
+            for (int b0 = 0; b0 < FP_T && !found; ++b0) {
+                if (!((rest >> b0) & 1u) || !colv(b0)) continue;
+                for (int b1 = b0 + 1; b1 < FP_T && !found; ++b1) {
+                    if (!((rest >> b1) & 1u) || !colv(b1) || colv(b1) == colv(b0)) continue;
+                    for (int b2 = b1 + 1; b2 < FP_T && !found; ++b2) {
+                        if (!((rest >> b2) & 1u) || !colv(b2)) continue;
+                        const uint32_t c2 = colv(b2);
+                        if (c2 == colv(b0) || c2 == colv(b1) || c2 == (colv(b0) ^ colv(b1))) continue;
+                        tpos[nt++] = b0;
+                        tpos[nt++] = b1;
+                        tpos[nt++] = b2;
+                        rest &= ~((1u << b0) | (1u << b1) | (1u << b2));
+                        found = true;
                     }
+                }
+            }
         }
         for (int b = 0; b < FP_T; ++b)
             if ((rest >> b) & 1u) tpos[nt++] = b;
@@ -1538,11 +1622,11 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
         }
         if (tabs.size() / FP_NT >= FP_MAX_TABS) return QSV_OK;
         ph.tab = (uint16_t)(tabs.size() / FP_NT);
-        for (int t = 0; t < FP_NT; ++t) tabs.push_back((uint16_t)fp_swz(base_of[t]));
+        for (int t = 0; t < FP_NT; ++t) tabs.push_back((uint16_t)fp_swz(A(base_of[t])));
         auto slot_mask = [&](int nib) {
             uint32_t m = 0;
             for (int j = 0; j < 4; ++j)
-                if ((nib >> j) & 1) m ^= fp_swz(1u << rpos[j]);
+                if ((nib >> j) & 1) m ^= fp_swz(A.col[rpos[j]]);
             return (uint16_t)(m << 4);
         };
         // compose the leading / trailing permutations into one map of the 16 register slots
@@ -1688,12 +1772,23 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
             ++cnt;
         }
         ph.nsub = (uint8_t)cnt;
+        for (size_t i = 0; i < ps.sel.size(); ++i)
+            if (ps.role[i] == 4) absorb(ops[ps.sel[i]]);  // the data stays put; later readers use the new map
     }
     for (int r = 0; r < 16; ++r) {
         uint64_t o = 0;
         for (int j = 0; j < 4; ++j)
             if ((r >> j) & 1) o |= 1ull << P.pos[8 + j];
         P.row_off[r] = o * sizeof(double2);
+    }
+    // copy-out (passes without a direct-store phase): tile index (row r, thread t) is read from
+    // slot fp_swz(A(t)) ^ fp_swz(A.col-part of r << 8)
+    for (int r = 0; r < 16; ++r) P.out_row[r] = (uint16_t)(fp_swz(A((uint32_t)r << 8) ^ A.off) << 4);
+    P.out_tab = 0xffff;
+    if (!is_identity()) {
+        if (tabs.size() / FP_NT >= FP_MAX_TABS) return QSV_OK;
+        P.out_tab = (uint16_t)(tabs.size() / FP_NT);
+        for (int t = 0; t < FP_NT; ++t) tabs.push_back((uint16_t)fp_swz(A((uint32_t)t)));
     }
     // runs of consecutive non-tile index bits: tile number bits [src, src+len) land at [dst, dst+len)
     P.nseg = 0;
