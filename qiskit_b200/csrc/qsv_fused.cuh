@@ -31,7 +31,7 @@
 #define FP_MAX_DIAGS 40  // diagonal ops per pass
 #define FP_NOCOEF 0xffffffffu
 
-enum { FP_D1C = 0, FP_D1R = 1, FP_D2C = 2, FP_D2R = 3, FP_DIAG = 4 };
+enum { FP_D1C = 0, FP_D1R = 1, FP_D2C = 2, FP_D2R = 3, FP_DIAG = 4, FP_DIAGU = 5 };
 
 struct FpPhase {           // 80 bytes
     uint16_t rd[16];       // register r is read from byte offset (thread offset ^ rd[r]) of the tile buffer
@@ -233,6 +233,11 @@ __device__ __forceinline__ void fp_apply(double2 (&v)[16], const FpPass& P, int 
         case FP_D2R * 16 + 9: fp_d2r<1, 2>(v, P, mo); break;
         case FP_D2R * 16 + 13: fp_d2r<1, 3>(v, P, mo); break;
         case FP_D2R * 16 + 14: fp_d2r<2, 3>(v, P, mo); break;
+        case FP_DIAGU * 16: {  // register-bit factor of a separable diagonal: 16 uniform coefficients
+#pragma unroll
+            for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], make_double2(P.mats[mo + 2 * r], P.mats[mo + 2 * r + 1]));
+            break;
+        }
         default: fp_diag(v, P, mo, tabs_sm, tile_base, t); break;
     }
 }

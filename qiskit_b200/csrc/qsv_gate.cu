@@ -242,7 +242,7 @@ __global__ void __launch_bounds__(NT, 512 / NT) k_tile_pass(double2* __restrict_
 // per-phase gathers are free of bank conflicts (host picks the lane bits accordingly).
 #define CL_R 4
 #define CL_REGS (1 << CL_R)
-enum { CL_DENSE1 = 0, CL_DENSE1R = 1, CL_DENSE2 = 2, CL_DENSE2R = 3, CL_DIAG = 4, CL_MONO = 5 };
+enum { CL_DENSE1 = 0, CL_DENSE1R = 1, CL_DENSE2 = 2, CL_DENSE2R = 3, CL_DIAG = 4, CL_MONO = 5, CL_DIAGU = 6 };
 
 struct ClSub {                 // 64 bytes
     uint8_t kind, k;
@@ -1699,13 +1699,79 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
         }
         ph.sub_first = (uint16_t)nsubs;
         int cnt = 0;
+        // ops of this phase; a diagonal table that factors into (register bits) x (all other bits) is
+        // split: the register factor is 16 uniform coefficients from the constant bank, the rest is ONE
+        // table lookup per thread -- instead of 16 scattered 16-byte loads per thread through L1
+        std::vector<TileOp> pops;
         for (size_t i = 0; i < ps.sel.size(); ++i) {
             if (ps.role[i]) continue;
             const TileOp& op = ops[ps.sel[i]];
+            uint32_t regm = 0;  // table index bits fed by register bits
+            if (op.kind == CL_DIAG && s->use_diag_split)
+                for (int j = 0; j < op.k; ++j)
+                    if (op.bits[j] < 64 && ((S >> op.bits[j]) & 1u)) regm |= 1u << j;
+            bool split = regm != 0 && op.m[0] != cplx(0.0, 0.0);
+            if (split) {
+                const cplx t0 = op.m[0];
+                for (size_t x = 0; x < op.m.size() && split; ++x) {
+                    const cplx lhs = op.m[x] * t0, rhs = op.m[x & regm] * op.m[x & ~(size_t)regm];
+                    split = std::abs(lhs - rhs) <= 1e-14 * std::max(1.0, std::abs(lhs));
+                }
+            }
+            if (!split) {
+                pops.push_back(op);
+                continue;
+            }
+            TileOp u;
+            memset(u.bits, 0, sizeof u.bits);
+            memset(u.src, 0, sizeof u.src);
+            u.unit = false;
+            u.kind = CL_DIAGU;
+            u.k = 4;
+            u.m.assign(16, cplx(1.0, 0.0));
+            for (int r = 0; r < 16; ++r) {
+                size_t x = 0;
+                for (int j = 0; j < op.k; ++j)
+                    if ((regm >> j) & 1u) x |= (size_t)((r >> rank_in(S, op.bits[j])) & 1) << j;
+                u.m[r] = op.m[x];
+            }
+            pops.push_back(std::move(u));
+            TileOp rest;
+            memset(rest.bits, 0, sizeof rest.bits);
+            memset(rest.src, 0, sizeof rest.src);
+            rest.unit = false;
+            rest.kind = CL_DIAG;
+            rest.k = 0;
+            int jmap[DIAG_MAX_BITS];
+            for (int j = 0; j < op.k; ++j)
+                if (!((regm >> j) & 1u)) {
+                    jmap[rest.k] = j;
+                    rest.bits[rest.k++] = op.bits[j];
+                }
+            rest.m.assign((size_t)1 << rest.k, cplx(1.0, 0.0));
+            bool trivial = true;
+            for (size_t y = 0; y < rest.m.size(); ++y) {
+                size_t x = 0;
+                for (int jj = 0; jj < rest.k; ++jj) x |= ((y >> jj) & 1) << jmap[jj];
+                rest.m[y] = op.m[x] / op.m[0];
+                trivial &= rest.m[y] == cplx(1.0, 0.0);
+            }
+            if (!trivial) pops.push_back(std::move(rest));
+        }
+        for (size_t i = 0; i < pops.size(); ++i) {
+            const TileOp& op = pops[i];
             if (nsubs >= FP_MAX_SUBS || cnt >= 255) return QSV_OK;
             FpSub& sb = P.subs[nsubs];
             memset(&sb, 0, sizeof sb);
-            if (op.kind == CL_DIAG) {
+            if (op.kind == CL_DIAGU) {
+                if (nmat + 32 > FP_MAX_MAT) return QSV_OK;
+                sb.kind = FP_DIAGU;
+                sb.mat = (uint16_t)nmat;
+                for (int r = 0; r < 16; ++r) {
+                    P.mats[nmat++] = op.m[r].real();
+                    P.mats[nmat++] = op.m[r].imag();
+                }
+            } else if (op.kind == CL_DIAG) {
                 if (tabs.size() / FP_NT >= FP_MAX_TABS || diags.size() >= FP_MAX_DIAGS) return QSV_OK;
                 FpDiag d;
                 memset(&d, 0, sizeof d);
@@ -1826,7 +1892,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
 }
 
 static void trace_fused_pass(const FpPass& P, FILE* f) {
-    int cnt[5] = {0, 0, 0, 0, 0};
+    int cnt[6] = {0, 0, 0, 0, 0, 0};
     fprintf(f, "[fused] T bits:");
     for (int b = 0; b < FP_T; ++b) fprintf(f, " %d", P.pos[b]);
     fprintf(f, " | %sphases %d:", P.warp_local ? "warp-local " : "", P.nphases);
@@ -1835,7 +1901,8 @@ static void trace_fused_pass(const FpPass& P, FILE* f) {
                 P.phases[p].rcoef != FP_NOCOEF ? "r" : "", P.phases[p].wcoef != FP_NOCOEF ? "w" : "");
         for (int i = 0; i < P.phases[p].nsub; ++i) cnt[P.subs[P.phases[p].sub_first + i].kind]++;
     }
-    fprintf(f, " | d1c %d d1r %d d2c %d d2r %d diag %d | tabs %d\n", cnt[0], cnt[1], cnt[2], cnt[3], cnt[4], P.ntabs);
+    fprintf(f, " | d1c %d d1r %d d2c %d d2r %d diag %d diagu %d | tabs %d\n", cnt[0], cnt[1], cnt[2], cnt[3], cnt[4], cnt[5],
+            P.ntabs);
 }
 
 static int launch_fused_pass(qsv_state* s, const FpPass& P) {

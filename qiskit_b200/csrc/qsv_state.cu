@@ -79,6 +79,7 @@ void qsv_state_defaults(qsv_state* s) {
     s->use_direct_store = env_int("QSV_DIRECT_STORE", 1);
     s->use_fused3 = env_int("QSV_FUSED3", 0);
     s->use_linear_perm = env_int("QSV_LINEAR_PERM", 1);
+    s->use_diag_split = env_int("QSV_DIAG_SPLIT", 1);
     s->lazy_init = env_int("QSV_LAZY_INIT", 1);
     s->use_product_init = env_int("QSV_PRODUCT_INIT", 1);
     s->use_warp_local = env_int("QSV_WARP_LOCAL", 0);  // measured: no gain (barriers are not the limiter), and its 32-byte store segments cost 20 %
@@ -178,6 +179,7 @@ extern "C" int qsv_clone(const qsv_state* s, qsv_state** out) {
     c->use_warp_local = s->use_warp_local;
     c->use_fused3 = s->use_fused3;
     c->use_linear_perm = s->use_linear_perm;
+    c->use_diag_split = s->use_diag_split;
     c->lazy_init = s->lazy_init;
     c->use_product_init = s->use_product_init;
     QSV_TRY(qsv_materialize(const_cast<qsv_state*>(s)));
@@ -341,6 +343,8 @@ extern "C" int qsv_set_option(qsv_state* s, const char* name, int64_t value) {
         s->use_fused3 = value != 0;
     } else if (!strcmp(name, "linear_perm")) {
         s->use_linear_perm = value != 0;
+    } else if (!strcmp(name, "diag_split")) {
+        s->use_diag_split = value != 0;
     } else if (!strcmp(name, "product_init")) {
         s->use_product_init = value != 0;
     } else if (!strcmp(name, "lazy_init")) {
