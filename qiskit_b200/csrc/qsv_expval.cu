@@ -454,7 +454,20 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
         bool have_copy = false;
         const double r2 = 0.70710678118654752440;
         for (QwcGroup* g : rotated) {
-            if (!have_copy) {
+            // Two ways to reach this family's frame: keep rotating the scratch copy in place, or start
+            // again from the state itself (out of place, no copy).  From the Z frame every rotation is
+            // a real H, preceded by a diagonal S^dagger for Y -- half the FP64 work of the complex
+            // X <-> Y change of frame -- so restart whenever that does not take more passes.
+            auto frame_of = [](uint64_t xb, uint64_t zb, uint64_t b) { return (xb & b) ? ((zb & b) ? 2 : 1) : 0; };
+            int n_cur = 0, n_psi = 0;
+            for (int q = 0; q < s->n_local; ++q) {
+                const uint64_t b = 1ull << q;
+                const int want = frame_of(g->xb, g->zb, b);
+                n_cur += want != frame_of(cur_x, cur_z, b);
+                n_psi += want != 0;
+            }
+            auto passes_for = [](int nq) { return nq <= 0 ? 0 : (nq <= 12 ? 1 : 1 + (nq - 12 + 7) / 8); };
+            if (!have_copy || passes_for(n_psi) <= passes_for(n_cur)) {
                 // no copy: the first rotation pass reads the state and writes the scratch buffer
                 aux->read_from = s->amp;
                 have_copy = true;
@@ -464,25 +477,34 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
             std::vector<HGate> layer;
             for (int q = 0; q < s->n_local; ++q) {
                 const uint64_t b = 1ull << q;
-                const int want = (g->xb & b) ? ((g->zb & b) ? 2 : 1) : 0;           // 0 Z/unset, 1 X, 2 Y
-                const int have = (cur_x & b) ? ((cur_z & b) ? 2 : 1) : 0;
+                const int want = frame_of(g->xb, g->zb, b);
+                const int have = frame_of(cur_x, cur_z, b);
                 if (want == have) continue;
                 const cplx I(0.0, 1.0);
                 cplx vx[4] = {r2, r2, r2, -r2};                       // H
                 cplx vy[4] = {r2, -I * r2, r2, I * r2};               // H S^dagger
                 cplx id[4] = {1.0, 0.0, 0.0, 1.0};
-                const cplx* vn = want == 1 ? vx : (want == 2 ? vy : id);
-                const cplx* vc = have == 1 ? vx : (have == 2 ? vy : id);
                 HGate hg;
                 hg.k = 1;
                 memset(hg.q, 0, sizeof hg.q);
                 hg.q[0] = q;
+                if (have == 0 && want == 2) {  // S^dagger as a diagonal gate (joins the pass's phase table), then H
+                    hg.diag = true;
+                    hg.m = {cplx(1.0, 0.0), -I};
+                    layer.push_back(hg);
+                }
                 hg.diag = false;
                 hg.m.resize(4);
-                for (int r = 0; r < 2; ++r)
-                    for (int c = 0; c < 2; ++c)  // (vn * vc^dagger)[r][c] = sum_k vn[r][k] conj(vc[c][k])
-                        hg.m[r * 2 + c] = vn[r * 2 + 0] * std::conj(vc[c * 2 + 0]) +
-                                          vn[r * 2 + 1] * std::conj(vc[c * 2 + 1]);
+                if (have == 0) {
+                    for (int i = 0; i < 4; ++i) hg.m[i] = vx[i];
+                } else {
+                    const cplx* vn = want == 1 ? vx : (want == 2 ? vy : id);
+                    const cplx* vc = have == 1 ? vx : vy;
+                    for (int r = 0; r < 2; ++r)
+                        for (int c = 0; c < 2; ++c)  // (vn * vc^dagger)[r][c] = sum_k vn[r][k] conj(vc[c][k])
+                            hg.m[r * 2 + c] = vn[r * 2 + 0] * std::conj(vc[c * 2 + 0]) +
+                                              vn[r * 2 + 1] * std::conj(vc[c * 2 + 1]);
+                }
                 layer.push_back(hg);
                 cur_x = (cur_x & ~b) | ((want ? b : 0));
                 cur_z = (cur_z & ~b) | ((want == 2 ? b : 0));
