@@ -146,6 +146,50 @@ int qsv_collapse(qsv_state* s, const int* qargs, int m, uint64_t outcome, double
 int qsv_pack_samples(const uint64_t* indices, uint64_t shots, const int* src_bit, int num_bits,
                      uint8_t* out);
 
+/* ---- index-gather ops on whole states (single-GPU handles) ---- */
+/* dst[i] = src[j] where bit src_bit[k] of j equals bit k of i (k < n).  Covers
+ * Statevector.reverse_qargs (statevector.py:512-531), the layout permutation of
+ * Statevector.from_circuit (:115-180) and DensityMatrix.reverse_qargs /
+ * partial_transpose (densitymatrix.py:344-364, 839-866).  dst != src. */
+int qsv_permute_qubits(qsv_state* dst, const qsv_state* src, const int* src_bit);
+/* dst[i] = a[ia] * (conj_b ? conj(b[ib]) : b[ib]), bit j of ia = bit a_pos[j] of i
+ * and bit j of ib = bit b_pos[j] of i.  Statevector.tensor / expand
+ * (statevector.py:339-397: np.kron), DensityMatrix.tensor / expand
+ * (densitymatrix.py:229-265) and the projector |v><v| of DensityMatrix.__init__
+ * (densitymatrix.py:104: np.outer(v, conj(v))). */
+int qsv_tensor(qsv_state* dst, const qsv_state* a, const qsv_state* b, const int* a_pos,
+               const int* b_pos, int conj_b);
+/* dst <- dst + (re + i im) * src: Statevector._add / DensityMatrix._add
+ * (statevector.py:399-413, densitymatrix.py:267-285) without a host round trip */
+int qsv_axpy(qsv_state* dst, const qsv_state* src, double re, double im);
+/* element-wise complex conjugate in place: Statevector.conjugate (statevector.py:327-329),
+ * DensityMatrix.conjugate (densitymatrix.py:213-215) */
+int qsv_conjugate(qsv_state* s);
+
+/* ---- density matrices ------------------------------------ */
+/* A DensityMatrix of n qubits is held as the 2n-qubit handle whose amplitude
+ * index is (row << n) | col, i.e. the C-order ravel of rho (densitymatrix.py
+ * keeps rho as a 2^n x 2^n array).  Evolution rho -> U rho U^dagger
+ * (densitymatrix.py:720-750) is qsv_apply_gates with U on qubits q + n and
+ * conj(U) on qubits q.  All entry points below need an even-qubit handle. */
+/* density_expval_pauli_no_x / density_expval_pauli_with_x
+ * (crates/accelerate/src/pauli_exp_val.rs:128-154, :159-194), one value per term:
+ * x_mask == 0: sum_i s_i Re rho[i][i];  else 2 * sum_{i0} s_i0 Re(phase * rho[i0 ^ x][i0])
+ * over the i0 with bit x_max(x_mask) clear; s = (-1)^popcount(i & z_mask);
+ * phases[t] = (-i)^(#Y_t).  The F-order ravel at densitymatrix.py:388 is folded
+ * into the index arithmetic. */
+int qsv_density_expval_pauli_batch(const qsv_state* s, uint64_t n_terms, const uint64_t* z_masks,
+                                   const uint64_t* x_masks, const double* phases_c128, double* out);
+/* DensityMatrix.probabilities (densitymatrix.py:498-506): |diag| -> marginal with
+ * output bit j = qubit qargs[j] -> clip to [0, 1]; qargs == NULL: all qubits */
+int qsv_density_probabilities(const qsv_state* s, const int* qargs, int m, double* host_out);
+/* DensityMatrix.trace (:217-219) and purity (:221-227: trace(rho . rho)) */
+int qsv_density_trace(const qsv_state* s, double* out_c128);
+int qsv_density_purity(const qsv_state* s, double* out_c128);
+/* DensityMatrix.reset(qargs) (densitymatrix.py:508-537): the reset SuperOp, i.e.
+ * rho' = sum_k (|0><k| on qargs) rho (|k><0| on qargs) */
+int qsv_density_reset(qsv_state* s, const int* qargs, int m);
+
 /* ---- measurement hooks -------------------------------------------------- */
 int qsv_get_counters(const qsv_state* s, qsv_counters* out);
 int qsv_reset_counters(qsv_state* s);

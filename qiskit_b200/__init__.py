@@ -11,11 +11,12 @@ from .circuit import (ClassicalRegister, Gate, Instruction, Parameter, Parameter
                       QuantumCircuit)
 from .pauli import Pauli, PauliList, SparsePauliOp
 from .statevector import Statevector
+from .densitymatrix import DensityMatrix
 from .primitives import BitArray, StatevectorEstimator, StatevectorSampler
 
 __all__ = [
     "QiskitError", "QuantumCircuit", "ClassicalRegister", "Parameter", "ParameterVector", "Gate",
-    "Instruction", "Pauli", "PauliList", "SparsePauliOp", "Statevector", "StatevectorEstimator",
+    "Instruction", "Pauli", "PauliList", "SparsePauliOp", "Statevector", "DensityMatrix", "StatevectorEstimator",
     "StatevectorSampler", "BitArray", "install",
 ]
 __version__ = "0.1.0"

@@ -78,6 +78,15 @@ PROTOTYPES = {
     "qsv_sample": (_i, [_vp, _P(_i), _i, _vp, _u64, _vp, _P(_dbl)]),
     "qsv_collapse": (_i, [_vp, _P(_i), _i, _u64, _dbl, _i]),
     "qsv_pack_samples": (_i, [_vp, _u64, _P(_i), _i, _vp]),
+    "qsv_permute_qubits": (_i, [_vp, _vp, _P(_i)]),
+    "qsv_tensor": (_i, [_vp, _vp, _vp, _P(_i), _P(_i), _i]),
+    "qsv_axpy": (_i, [_vp, _vp, _dbl, _dbl]),
+    "qsv_conjugate": (_i, [_vp]),
+    "qsv_density_expval_pauli_batch": (_i, [_vp, _u64, _vp, _vp, _vp, _vp]),
+    "qsv_density_probabilities": (_i, [_vp, _P(_i), _i, _vp]),
+    "qsv_density_trace": (_i, [_vp, _P(_dbl)]),
+    "qsv_density_purity": (_i, [_vp, _P(_dbl)]),
+    "qsv_density_reset": (_i, [_vp, _P(_i), _i]),
     "qsv_get_counters": (_i, [_vp, _P(QsvCounters)]),
     "qsv_reset_counters": (_i, [_vp]),
     "qsv_timer_begin": (_i, [_vp]),
