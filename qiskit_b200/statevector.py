@@ -223,6 +223,18 @@ class Statevector:
         """statevector.py:818-843."""
         return cls(instruction, device=device)
 
+    @classmethod
+    def from_circuit(cls, circuit, ignore_set_layout: bool = False, *, device: int = 0):
+        """statevector.py:115-180: simulate, then undo the transpiler's final layout: new qubit k
+        takes old qubit ``final_index_layout()[k]`` (the reference's tensor transpose with
+        ``reversed_perm``), as one bit-permutation kernel."""
+        layout = None if ignore_set_layout else getattr(circuit, "layout", None)
+        sv = cls.from_instruction(circuit, device=device)
+        if layout is None:
+            return sv
+        idx = [int(v) for v in layout.final_index_layout()]
+        return sv._permuted(idx)
+
     # ------------------------------------------------------------- algebra --
     def is_valid(self, atol=None, rtol=None):
         atol = self.atol if atol is None else atol
@@ -241,9 +253,48 @@ class Statevector:
         return self._norm2() ** 2
 
     def conjugate(self):
+        """statevector.py:327-329, element-wise on the device."""
         ret = self._new_like()
-        ret._upload(np.conj(self.data))
+        _lib.check(_lib.load().qsv_conjugate(ret._h))
         return ret
+
+    def _kron(self, hi: "Statevector", lo: "Statevector"):
+        """np.kron(hi, lo) on the device: ``lo`` takes the low qubits."""
+        n = hi._n + lo._n
+        ret = object.__new__(type(self))
+        ret._rng_generator = self._rng_generator
+        ret._device = self._device
+        ret._n = n
+        ret._h = _lib.acquire(n, self._device)
+        _lib.check(_lib.load().qsv_tensor(ret._h, hi._h, lo._h, _lib.int_array(range(lo._n, n)),
+                                          _lib.int_array(range(lo._n)), 0))
+        return ret
+
+    def tensor(self, other):
+        """statevector.py:339-360: self (x) other."""
+        if not isinstance(other, Statevector):
+            other = Statevector(other, device=self._device)
+        return self._kron(self, other)
+
+    def expand(self, other):
+        """statevector.py:378-397: other (x) self."""
+        if not isinstance(other, Statevector):
+            other = Statevector(other, device=self._device)
+        return self._kron(other, self)
+
+    def _permuted(self, src_bit):
+        """New state with amplitude i taken from index j, bit src_bit[k] of j = bit k of i."""
+        ret = object.__new__(type(self))
+        ret._rng_generator = self._rng_generator
+        ret._device = self._device
+        ret._n = self._n
+        ret._h = _lib.acquire(self._n, self._device)
+        _lib.check(_lib.load().qsv_permute_qubits(ret._h, self._h, _lib.int_array(src_bit)))
+        return ret
+
+    def reverse_qargs(self):
+        """statevector.py:512-531: qubit q <-> n-1-q."""
+        return self._permuted([self._n - 1 - k for k in range(self._n)])
 
     def inner(self, other) -> complex:
         """<self|other> (statevector.py:399-413)."""
@@ -276,13 +327,17 @@ class Statevector:
         if not isinstance(other, Statevector) or other._n != self._n:
             raise QiskitError("other is not a Statevector of the same size")
         ret = self._new_like()
-        ret._upload(self.data + other.data)  # host round trip: not on the simulation path
+        _lib.check(_lib.load().qsv_axpy(ret._h, other._h, 1.0, 0.0))
         return ret
 
     __add__ = _add
 
     def __sub__(self, other):
-        return self._add(-other)
+        if not isinstance(other, Statevector) or other._n != self._n:
+            raise QiskitError("other is not a Statevector of the same size")
+        ret = self._new_like()
+        _lib.check(_lib.load().qsv_axpy(ret._h, other._h, -1.0, 0.0))
+        return ret
 
     def equiv(self, other, rtol=None, atol=None) -> bool:
         """Equal up to a global phase (statevector.py:480-510)."""
