@@ -190,6 +190,26 @@ int qsv_density_purity(const qsv_state* s, double* out_c128);
  * rho' = sum_k (|0><k| on qargs) rho (|k><0| on qargs) */
 int qsv_density_reset(qsv_state* s, const int* qargs, int m);
 
+/* ---- counts post-processing (handle-less: device id + host arrays) ---- */
+/* bitstring_expval of crates/accelerate/src/sampled_exp_val.rs:46-67 for every term of a
+ * diagonal operator over {I, Z, 0, 1}: out[t] = sum_k w[k] * prod_q d_q(bit q of keys[k]) / sum_k w[k]
+ * with d = (+1, -1) on z_mask bits, (1, 0) on zero_mask bits, (0, 1) on one_mask bits.
+ * keys = outcomes as integers (bit q = clbit / qubit q), weights = their counts or
+ * quasi-probabilities (NULL: every key is one shot).  Used by sampled_expectation_value
+ * (qiskit/result/sampled_expval.py:37-91) and BitArray.expectation_values
+ * (primitives/containers/bit_array.py:613-656). */
+int qsv_sampled_expval(int device, const uint64_t* keys, const double* weights, uint64_t n_keys,
+                       uint64_t n_terms, const uint64_t* z_masks, const uint64_t* zero_masks,
+                       const uint64_t* one_masks, double* out);
+/* out[i] bit j = keys[i] bit src_bit[j] (src_bit[j] < 0: 0): marginal_counts / marginal_memory
+ * (crates/accelerate/src/results/marginalization.rs) and BitArray.slice_bits on integer outcomes */
+int qsv_marginalize_samples(int device, const uint64_t* keys, uint64_t n, const int* src_bit, int m,
+                            uint64_t* out);
+/* np.unique(samples, return_counts=True) of QuantumState.sample_counts (quantum_state.py:291-293)
+ * and BitArray.get_int_counts: out_keys ascending, out_counts their multiplicities; both sized n */
+int qsv_sample_counts(int device, const uint64_t* keys, uint64_t n, uint64_t* out_keys, uint64_t* out_counts,
+                      uint64_t* n_unique);
+
 /* ---- measurement hooks -------------------------------------------------- */
 int qsv_get_counters(const qsv_state* s, qsv_counters* out);
 int qsv_reset_counters(qsv_state* s);

@@ -13,11 +13,13 @@ from .pauli import Pauli, PauliList, SparsePauliOp
 from .statevector import Statevector
 from .densitymatrix import DensityMatrix
 from .primitives import BitArray, StatevectorEstimator, StatevectorSampler
+from .basic_simulator import BasicSimulator
+from .sampled_expval import sampled_expectation_value
 
 __all__ = [
     "QiskitError", "QuantumCircuit", "ClassicalRegister", "Parameter", "ParameterVector", "Gate",
     "Instruction", "Pauli", "PauliList", "SparsePauliOp", "Statevector", "DensityMatrix", "StatevectorEstimator",
-    "StatevectorSampler", "BitArray", "install",
+    "StatevectorSampler", "BitArray", "BasicSimulator", "sampled_expectation_value", "install",
 ]
 __version__ = "0.1.0"
 

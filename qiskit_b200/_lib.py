@@ -87,6 +87,9 @@ PROTOTYPES = {
     "qsv_density_trace": (_i, [_vp, _P(_dbl)]),
     "qsv_density_purity": (_i, [_vp, _P(_dbl)]),
     "qsv_density_reset": (_i, [_vp, _P(_i), _i]),
+    "qsv_sampled_expval": (_i, [_i, _vp, _vp, _u64, _u64, _vp, _vp, _vp, _vp]),
+    "qsv_marginalize_samples": (_i, [_i, _vp, _u64, _P(_i), _i, _vp]),
+    "qsv_sample_counts": (_i, [_i, _vp, _u64, _vp, _vp, _P(_u64)]),
     "qsv_get_counters": (_i, [_vp, _P(QsvCounters)]),
     "qsv_reset_counters": (_i, [_vp]),
     "qsv_timer_begin": (_i, [_vp]),

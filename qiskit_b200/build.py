@@ -12,7 +12,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libqsv_b200.so")
-SOURCES = ["qsv_state.cu", "qsv_gate.cu", "qsv_expval.cu", "qsv_sample.cu", "qsv_dist.cu", "qsv_density.cu"]
+SOURCES = ["qsv_state.cu", "qsv_gate.cu", "qsv_expval.cu", "qsv_sample.cu", "qsv_dist.cu", "qsv_density.cu", "qsv_counts.cu"]
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
     "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "--shared", "-cudart", "static",

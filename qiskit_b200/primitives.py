@@ -159,6 +159,85 @@ class BitArray:
     def get_counts(self, loc=None) -> dict:
         return {format(k, f"0{self._num_bits}b"): v for k, v in self.get_int_counts(loc).items()}
 
+    def slice_bits(self, indices):
+        """bit_array.py:515-548: keep the listed bit positions (bit 0 = least significant), in
+        order; the gather runs on the device over the integer outcomes."""
+        from .sampled_expval import marginalize_samples
+
+        idx = [int(indices)] if isinstance(indices, (int, np.integer)) else [int(i) for i in indices]
+        if any(i < 0 or i >= self._num_bits for i in idx):
+            raise IndexError("index is out of bounds")
+        if self._num_bits > 64:
+            raise ValueError("slice_bits on more than 64 bits is outside the device path")
+        vals = marginalize_samples(self._ints().astype(np.uint64), idx)
+        nbytes = (len(idx) + 7) // 8
+        out = np.zeros((vals.size, nbytes), dtype=np.uint8)
+        for b in range(nbytes):
+            out[:, nbytes - 1 - b] = (vals >> np.uint64(8 * b)) & np.uint64(255)
+        return BitArray(out.reshape(self.shape + (self.num_shots, nbytes)), len(idx))
+
+    def expectation_values(self, observables, *, device: int = 0) -> np.ndarray:
+        """bit_array.py:613-656: expectation values of diagonal observables (I, Z, 0, 1),
+        broadcast against this array's shape; real part, as ``sampled_expectation_value``.
+        Every position's shots go to the device once with all the labels that need them."""
+        from .sampled_expval import OPERS, _device_expvals, _oper_terms
+
+        def is_leaf(o):
+            return isinstance(o, (str, dict)) or hasattr(o, "paulis") or (hasattr(o, "z") and hasattr(o, "x"))
+
+        def to_terms(o):
+            if isinstance(o, dict):
+                labels, coeffs = [k.upper() for k in o], np.asarray(list(o.values()))
+            else:
+                labels, coeffs = _oper_terms(o)
+            for lab in labels:
+                if len(lab) != self._num_bits:
+                    raise ValueError(
+                        f"The number of qubits of the observable ({len(lab)}) does not match "
+                        f"the number of bits of the bit array ({self._num_bits})"
+                    )
+                if set(lab).difference(OPERS):
+                    raise ValueError(f"Input operator {lab} is not diagonal")
+            return labels, coeffs
+
+        def build(o):  # nested lists -> object ndarray of (labels, coeffs), like ObservablesArray.coerce
+            if is_leaf(o):
+                out = np.empty((), dtype=object)
+                out[()] = to_terms(o)
+                return out
+            subs = [build(x) for x in o]
+            if not subs or len({x.shape for x in subs}) != 1:
+                raise ValueError("ragged or empty observables array")
+            out = np.empty((len(subs),) + subs[0].shape, dtype=object)
+            for i, x in enumerate(subs):
+                out[i] = x[()] if x.ndim == 0 else x
+            return out
+
+        obs = build(observables)
+        if self._num_bits > 64:
+            raise ValueError("expectation_values on more than 64 bits is outside the device path")
+        arr_indices = np.fromiter(np.ndindex(self.shape), dtype=object, count=int(np.prod(self.shape, dtype=int)))
+        arr_indices = arr_indices.reshape(self.shape)
+        try:
+            bc_indices, bc_obs = np.broadcast_arrays(arr_indices, obs)
+        except ValueError as ex:
+            raise ValueError("observables shape is not broadcastable with the bit array") from ex
+        # one device call per position of the bit array: all labels any broadcast partner needs
+        need: dict = {}
+        for index in np.ndindex(bc_indices.shape):
+            need.setdefault(bc_indices[index], {}).update(dict.fromkeys(bc_obs[index][0]))
+        values: dict = {}
+        for loc, labels in need.items():
+            labels = list(labels)
+            samples = self._ints(loc).astype(np.uint64)
+            values[loc] = dict(zip(labels, _device_expvals(samples, None, labels, device)))
+        out = np.zeros(bc_indices.shape, dtype=float)
+        for index in np.ndindex(bc_indices.shape):
+            labels, coeffs = bc_obs[index]
+            vals = values[bc_indices[index]]
+            out[index] = float(np.real(sum(c * vals[lab] for lab, c in zip(labels, coeffs))))
+        return out
+
     def get_bitstrings(self, loc=None) -> list:
         return [format(int(v), f"0{self._num_bits}b") for v in self._ints(loc)]
 
