@@ -70,7 +70,6 @@ struct qsv_state {
     int use_linear_perm;   // fused pass: X/CX/SWAP-like permutations are absorbed by the tile-index -> slot map
     int use_diag_split;    // fused pass: separable diagonal tables -> uniform register factor + one lookup per thread
     int use_fused3;        // fused passes through k_fused_pass3 (one CTA per SM, two groups, three tile buffers)
-    int stagger_ns;        // k_fused_pass: the second CTA of every SM starts this many ns per phase late (breaks the lockstep of the two CTAs)
     int num_sms;
     qsv_counters ctr;
     // sharding

@@ -69,7 +69,6 @@ struct FpPass {
     int32_t nphases;
     int32_t ntabs;
     int32_t warp_local;    // phases exchange data inside warps only (__syncwarp between phases)
-    uint32_t stagger_ns;   // start delay of the second wave of CTAs (blockIdx >= gridDim / 2), see k_fused_pass
     int32_t pos[FP_T];     // ascending global bit position of tile bit b
     const uint16_t* tabs;  // [ntabs][256]
     const double2* gdata;  // diagonal tables and coefficient vectors
@@ -287,17 +286,6 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const dou
 
     uint32_t tile = blockIdx.x;
     if (tile >= P.ntiles) return;
-    // The two CTAs of an SM start in lockstep and nothing ever separates them (both slow down
-    // together on the shared FP64 pipe, both wait for HBM together): the second wave of CTAs
-    // starts half a tile period late so that one CTA computes while the other loads / stores.
-    if (P.stagger_ns && blockIdx.x >= (gridDim.x >> 1)) {
-        uint64_t t0, t1;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-        do {
-            __nanosleep(200);
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-        } while (t1 - t0 < P.stagger_ns);
-    }
     uint64_t tile_base = tile_base_of(tile);
     issue_load(tile_base);
     while (true) {

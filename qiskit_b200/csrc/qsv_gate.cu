@@ -1528,7 +1528,6 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
                 if (!((W >> b) & 1u)) ps.S |= 1u << b;
     }
     P.warp_local = W ? 1 : 0;
-    P.stagger_ns = s->stagger_ns > 0 ? (uint32_t)s->stagger_ns * (uint32_t)std::max<size_t>(1, sels.size()) : 0u;
 
     std::vector<uint16_t> tabs;
     std::vector<FpDiag> diags;
