@@ -338,6 +338,26 @@ def roofline_gate_stream(args, device) -> dict:
     _lib.check(qsv.qsv_timer_end(h, C.byref(ms2)))
     ctr2 = sv.counters()
     norm = sv._norm2()
+    # configs[2] on the same handle: QFT, then probabilities scan + 1e6 samples (host uniforms in,
+    # uint64 indices out: the qsv_sample C-ABI call, copies included)
+    qft = gate_list_to_stream(lib.named_to_matrices(lib.qft_named(n)))
+    arr3, cnt3 = qft.to_c()
+    uniforms = np.random.default_rng(123).random(1_000_000)
+    idx = np.empty(uniforms.size, dtype=np.uint64)
+    total = C.c_double()
+    ms3, ms4 = C.c_float(), C.c_float()
+    for it in range(2):  # first round warms up
+        _lib.check(qsv.qsv_init_basis(h, 0))
+        _lib.check(qsv.qsv_sync(h))
+        _lib.check(qsv.qsv_reset_counters(h))
+        _lib.check(qsv.qsv_timer_begin(h))
+        _lib.check(qsv.qsv_apply_gates(h, arr3, cnt3, 0))
+        _lib.check(qsv.qsv_timer_end(h, C.byref(ms3)))
+        ctr3 = sv.counters()
+        _lib.check(qsv.qsv_timer_begin(h))
+        _lib.check(qsv.qsv_sample(h, None, n, uniforms.ctypes.data, uniforms.size, idx.ctypes.data,
+                                  C.byref(total)))
+        _lib.check(qsv.qsv_timer_end(h, C.byref(ms4)))
     peak, peak_src = measured_peak()
     return {
         "bound": "hbm", "kernel": "k_direct2<false> (one dense 2-qubit gate per launch, register resident)",
@@ -353,6 +373,14 @@ def roofline_gate_stream(args, device) -> dict:
             "gates_per_s_fused_qv": cnt2 / (ms2.value / 1e3),
             "hbm_gbs_fused_qv": ctr2["state_passes"] * bytes_per_pass / (ms2.value / 1e3) / 1e9,
             "norm_after": norm,
+            "sampler": {
+                "workload": f"{n}q QFT ({cnt3} gates) + 1e6 shots (configs[2])",
+                "qft_ms": ms3.value, "qft_passes": int(ctr3["state_passes"]),
+                "qft_hbm_gbs": ctr3["state_passes"] * bytes_per_pass / (ms3.value / 1e3) / 1e9,
+                "sample_ms": ms4.value, "shots_per_s": uniforms.size / (ms4.value / 1e3),
+                "scan_hbm_gbs": 16.0 * (1 << n) / (ms4.value / 1e3) / 1e9,
+                "total_probability": total.value,
+            },
         },
     }
 

@@ -181,7 +181,9 @@ def acquire(n_qubits: int, device: int = 0):
     with _pool_lock:
         free = _pool.get((n_qubits, device))
         if free:
-            return free.pop()
+            h = free.pop()
+            lib.qsv_reset_counters(h)   # a recycled handle starts with clean counters, like a new one
+            return h
     h = C.c_void_p()
     status = lib.qsv_create(C.byref(h), int(n_qubits), int(device))
     if status == ERR_NOMEM:  # pooled handles of other sizes may be holding the memory

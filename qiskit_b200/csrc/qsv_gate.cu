@@ -1059,8 +1059,8 @@ struct TileOp {
     bool unit;
 };
 
-// classify the gates of one pass into tile ops (consecutive diagonal gates share one table)
-static int make_tile_ops(const std::vector<HGate>& gates, const PassPlan& plan, const int* local_of,
+// classify the gates of one pass into tile ops, pass order kept: consecutive diagonal gates share one table
+static int make_tile_ops_runs(const std::vector<HGate>& gates, const PassPlan& plan, const int* local_of,
                          std::vector<TileOp>& ops) {
     const std::vector<int>& ids = plan.gate_ids;
     size_t gi = 0;
@@ -1124,6 +1124,141 @@ static int make_tile_ops(const std::vector<HGate>& gates, const PassPlan& plan, 
         ops.push_back(std::move(op));
         ++gi;
     }
+    return QSV_OK;
+}
+
+// classify the gates of one pass into tile ops.
+//
+// Diagonal gates commute with each other and with every gate on other qubits, so each one may
+// slide forward to just before the next non-diagonal gate that shares a qubit with it (its
+// "barrier"; the end of the pass if there is none).  All diagonals with the same barrier are
+// merged there into as few phase tables of <= DIAG_MAX_BITS index bits as a greedy cover finds:
+// a table grows by the bit that completes the most not-yet-covered gates.  (A QFT pass has a
+// controlled-phase ladder from each of its 8 targets to all lower qubits: consecutive-run merging
+// gave 29 tables, this gives 7 in-tile tables + the 8 x 21 cross pairs in 5-by-5 tables.)
+static int make_tile_ops_regrouped(const std::vector<HGate>& gates, const PassPlan& plan, const int* local_of,
+                                   std::vector<TileOp>& ops) {
+    const std::vector<int>& ids = plan.gate_ids;
+    const size_t N = ids.size();
+    std::vector<uint64_t> qm(N, 0);
+    for (size_t i = 0; i < N; ++i)
+        for (int j = 0; j < gates[ids[i]].k; ++j) qm[i] |= 1ull << gates[ids[i]].q[j];
+    std::vector<std::vector<size_t>> pend(N + 1);
+    for (size_t i = 0; i < N; ++i) {
+        if (!gates[ids[i]].diag) continue;
+        if (popc64(qm[i]) > DIAG_MAX_BITS) QSV_FAIL(QSV_ERR_UNSUPPORTED, "diagonal gate wider than %d qubits", DIAG_MAX_BITS);
+        size_t bar = N;
+        for (size_t j = i + 1; j < N; ++j)
+            if (!gates[ids[j]].diag && (qm[j] & qm[i])) {
+                bar = j;
+                break;
+            }
+        pend[bar].push_back(i);
+    }
+    auto emit_table = [&](uint64_t um, const std::vector<size_t>& members) {
+        TileOp op;
+        memset(op.bits, 0, sizeof op.bits);
+        memset(op.src, 0, sizeof op.src);
+        op.unit = false;
+        int d = 0;
+        int bit_of[64];
+        for (int bb = 0; bb < 64; ++bb)
+            if ((um >> bb) & 1ull) {
+                bit_of[bb] = d;
+                op.bits[d++] = local_of[bb] >= 0 ? local_of[bb] : 64 + bb;  // 64 + global bit: outside the tile
+            }
+        op.kind = CL_DIAG;
+        op.k = d;
+        op.m.assign((size_t)1 << d, cplx(1.0, 0.0));
+        for (size_t t : members) {
+            const HGate& h = gates[ids[t]];
+            for (size_t i = 0; i < op.m.size(); ++i) {
+                int hi = 0;
+                for (int j = 0; j < h.k; ++j) hi |= (int)((i >> bit_of[h.q[j]]) & 1) << j;
+                op.m[i] *= h.m[hi];
+            }
+        }
+        ops.push_back(std::move(op));
+    };
+    auto emit_group = [&](std::vector<size_t>& rest) {
+        while (!rest.empty()) {
+            uint64_t um = qm[rest[0]];
+            while (popc64(um) < DIAG_MAX_BITS) {
+                uint64_t cand = 0;
+                for (size_t t : rest) cand |= qm[t] & ~um;
+                if (!cand) break;
+                int best = -1, best_gain = 0;
+                for (int bb = 0; bb < 64; ++bb) {
+                    if (!((cand >> bb) & 1ull)) continue;
+                    const uint64_t with = um | (1ull << bb);
+                    int gain = 0;
+                    for (size_t t : rest) gain += (qm[t] & ~um) && !(qm[t] & ~with);
+                    if (gain > best_gain) best_gain = gain, best = bb;
+                }
+                if (best >= 0) {
+                    um |= 1ull << best;
+                    continue;
+                }
+                // no single bit completes a gate: take the gate that misses the fewest bits, if it fits
+                size_t pick = rest.size();
+                int miss = 65;
+                for (size_t x = 0; x < rest.size(); ++x) {
+                    const int m = popc64(qm[rest[x]] & ~um);
+                    if (m > 0 && m < miss) miss = m, pick = x;
+                }
+                if (pick == rest.size() || popc64(um) + miss > DIAG_MAX_BITS) break;
+                um |= qm[rest[pick]];
+            }
+            std::vector<size_t> members, left;
+            for (size_t t : rest) (qm[t] & ~um ? left : members).push_back(t);
+            emit_table(um, members);
+            rest.swap(left);
+        }
+    };
+    for (size_t gi = 0; gi <= N; ++gi) {
+        if (!pend[gi].empty()) emit_group(pend[gi]);
+        if (gi == N || gates[ids[gi]].diag) continue;
+        const HGate& g = gates[ids[gi]];
+        TileOp op;
+        memset(op.bits, 0, sizeof op.bits);
+        memset(op.src, 0, sizeof op.src);
+        op.unit = false;
+        const int dim = 1 << g.k;
+        for (int j = 0; j < g.k && j < DIAG_MAX_BITS; ++j) op.bits[j] = local_of[g.q[j]];
+        op.k = g.k;
+        if (g.k <= 3 && mat_is_mono(g.m, dim, op.src)) {
+            op.kind = CL_MONO;
+            op.unit = true;
+            op.m.resize(dim);
+            for (int r = 0; r < dim; ++r) {
+                op.m[r] = g.m[(size_t)r * dim + op.src[r]];
+                op.unit &= (op.m[r] == cplx(1.0, 0.0));
+            }
+        } else if (g.k == 1 || g.k == 2) {
+            const bool real = mat_is_real(g.m);
+            op.kind = g.k == 1 ? (real ? CL_DENSE1R : CL_DENSE1) : (real ? CL_DENSE2R : CL_DENSE2);
+            op.m = g.m;
+        } else {
+            QSV_FAIL(QSV_ERR_UNSUPPORTED, "internal: dense %d-qubit gate reached the tile path", g.k);
+        }
+        ops.push_back(std::move(op));
+    }
+    return QSV_OK;
+}
+
+// the regrouped order is used only when it needs fewer phase tables than the pass order (a tie keeps
+// the pass order, whose tables line up with the gate layers: EfficientSU2's RZ layers stay as they were)
+static int make_tile_ops(const std::vector<HGate>& gates, const PassPlan& plan, const int* local_of,
+                         std::vector<TileOp>& ops) {
+    std::vector<TileOp> runs, regrouped;
+    QSV_TRY(make_tile_ops_runs(gates, plan, local_of, runs));
+    QSV_TRY(make_tile_ops_regrouped(gates, plan, local_of, regrouped));
+    auto tables = [](const std::vector<TileOp>& v) {
+        size_t c = 0;
+        for (const TileOp& o : v) c += o.kind == CL_DIAG;
+        return c;
+    };
+    ops = tables(regrouped) < tables(runs) ? std::move(regrouped) : std::move(runs);
     return QSV_OK;
 }
 
