@@ -834,6 +834,50 @@ static void fuse_gates(std::vector<HGate>& gates, int nbits) {
         if (!dead[i]) gates.push_back(std::move(out[i]));
 }
 
+// A dense complex one-qubit unitary costs 8 DFMA per amplitude; written as D2 . R . D1 with R real
+// (|U00| -|U10| ; |U10| |U00|) and D1, D2 diagonal phases it costs 4, and the diagonals join the
+// phase tables of the pass (shared by all register bits of a phase, merged with neighbouring RZ /
+// RZZ / CP gates).  RX = S^dagger RY S is the typical case (Trotter circuits).  Only exact
+// reconstructions are taken (unitary input, both |U00| and |U10| well away from 0).
+static void split_complex_1q(std::vector<HGate>& gates) {
+    static const bool enabled = !getenv("QSV_NO_ZYZ");
+    if (!enabled || gates.size() < 2) return;
+    std::vector<HGate> out;
+    out.reserve(gates.size() + 8);
+    for (HGate& g : gates) {
+        bool done = false;
+        if (g.k == 1 && !g.diag && g.m.size() == 4 && !mat_is_real(g.m)) {
+            const cplx u00 = g.m[0], u01 = g.m[1], u10 = g.m[2], u11 = g.m[3];
+            const double c = std::abs(u00), sn = std::abs(u10), c2 = std::abs(u11);
+            if (c > 1e-3 && sn > 1e-3 && c2 > 1e-3) {
+                const cplx q0 = u00 / c, q1 = u10 / sn, p1 = (u11 / c2) * std::conj(q1);
+                // reconstruction: (q0 c, -q0 s p1 ; q1 s, q1 c p1)
+                const double err = std::max(std::max(std::abs(q0 * c - u00), std::abs(-q0 * sn * p1 - u01)),
+                                            std::max(std::abs(q1 * sn - u10), std::abs(q1 * c * p1 - u11)));
+                if (err < 4e-16) {
+                    HGate d1, r, d2;
+                    d1.k = r.k = d2.k = 1;
+                    memset(d1.q, 0, sizeof d1.q);
+                    memset(r.q, 0, sizeof r.q);
+                    memset(d2.q, 0, sizeof d2.q);
+                    d1.q[0] = r.q[0] = d2.q[0] = g.q[0];
+                    d1.diag = d2.diag = true;
+                    r.diag = false;
+                    d1.m = {cplx(1.0, 0.0), p1};
+                    r.m = {cplx(c, 0.0), cplx(-sn, 0.0), cplx(sn, 0.0), cplx(c, 0.0)};
+                    d2.m = {q0, q1};
+                    out.push_back(std::move(d1));
+                    out.push_back(std::move(r));
+                    out.push_back(std::move(d2));
+                    done = true;
+                }
+            }
+        }
+        if (!done) out.push_back(std::move(g));
+    }
+    gates.swap(out);
+}
+
 struct PassPlan {
     std::vector<int> gate_ids;
     uint64_t qmask;
@@ -1130,30 +1174,50 @@ static int make_tile_ops_runs(const std::vector<HGate>& gates, const PassPlan& p
 // classify the gates of one pass into tile ops.
 //
 // Diagonal gates commute with each other and with every gate on other qubits, so each one may
-// slide forward to just before the next non-diagonal gate that shares a qubit with it (its
-// "barrier"; the end of the pass if there is none).  All diagonals with the same barrier are
-// merged there into as few phase tables of <= DIAG_MAX_BITS index bits as a greedy cover finds:
+// run anywhere between the non-diagonal gates that share a qubit with it.  The gates are collected
+// at as few points of the pass as possible and merged there into as few phase tables of <= DIAG_MAX_BITS index bits as a greedy cover finds:
 // a table grows by the bit that completes the most not-yet-covered gates.  (A QFT pass has a
 // controlled-phase ladder from each of its 8 targets to all lower qubits: consecutive-run merging
 // gave 29 tables, this gives 7 in-tile tables + the 8 x 21 cross pairs in 5-by-5 tables.)
 static int make_tile_ops_regrouped(const std::vector<HGate>& gates, const PassPlan& plan, const int* local_of,
-                                   std::vector<TileOp>& ops) {
+                                   std::vector<TileOp>& ops, bool stab) {
     const std::vector<int>& ids = plan.gate_ids;
     const size_t N = ids.size();
     std::vector<uint64_t> qm(N, 0);
     for (size_t i = 0; i < N; ++i)
         for (int j = 0; j < gates[ids[i]].k; ++j) qm[i] |= 1ull << gates[ids[i]].q[j];
+    // slot s = "just before gate s" (s = N: end of the pass).  A diagonal gate may run in any slot
+    // after the last earlier and up to the first later non-diagonal gate that shares a qubit with it.
+    // Fewest slots that stab every interval (earliest-deadline sweep) -> largest groups to merge.
     std::vector<std::vector<size_t>> pend(N + 1);
+    std::vector<size_t> lo(N, 0), hi(N, N), diag_ids;
     for (size_t i = 0; i < N; ++i) {
         if (!gates[ids[i]].diag) continue;
         if (popc64(qm[i]) > DIAG_MAX_BITS) QSV_FAIL(QSV_ERR_UNSUPPORTED, "diagonal gate wider than %d qubits", DIAG_MAX_BITS);
-        size_t bar = N;
         for (size_t j = i + 1; j < N; ++j)
             if (!gates[ids[j]].diag && (qm[j] & qm[i])) {
-                bar = j;
+                hi[i] = j;
                 break;
             }
-        pend[bar].push_back(i);
+        for (size_t j = i; j-- > 0;)
+            if (!gates[ids[j]].diag && (qm[j] & qm[i])) {
+                lo[i] = j + 1;
+                break;
+            }
+        diag_ids.push_back(i);
+    }
+    std::sort(diag_ids.begin(), diag_ids.end(), [&](size_t a, size_t b) { return hi[a] != hi[b] ? hi[a] < hi[b] : a < b; });
+    {
+        std::vector<char> placed(N, 0);
+        for (size_t a : diag_ids) {
+            if (placed[a]) continue;
+            const size_t slot = hi[a];
+            for (size_t b : diag_ids)
+                if (!placed[b] && (stab ? lo[b] <= slot : hi[b] == slot)) {  // hi[b] >= slot: diag_ids is sorted by hi
+                    placed[b] = 1;
+                    pend[slot].push_back(b);
+                }
+        }
     }
     auto emit_table = [&](uint64_t um, const std::vector<size_t>& members) {
         TileOp op;
@@ -1246,19 +1310,23 @@ static int make_tile_ops_regrouped(const std::vector<HGate>& gates, const PassPl
     return QSV_OK;
 }
 
-// the regrouped order is used only when it needs fewer phase tables than the pass order (a tie keeps
+// a regrouped order is used only when it needs fewer phase tables than the pass order (a tie keeps
 // the pass order, whose tables line up with the gate layers: EfficientSU2's RZ layers stay as they were)
 static int make_tile_ops(const std::vector<HGate>& gates, const PassPlan& plan, const int* local_of,
                          std::vector<TileOp>& ops) {
-    std::vector<TileOp> runs, regrouped;
+    std::vector<TileOp> runs, late, stabbed;
     QSV_TRY(make_tile_ops_runs(gates, plan, local_of, runs));
-    QSV_TRY(make_tile_ops_regrouped(gates, plan, local_of, regrouped));
+    QSV_TRY(make_tile_ops_regrouped(gates, plan, local_of, late, false));    // every gate at its latest slot
+    QSV_TRY(make_tile_ops_regrouped(gates, plan, local_of, stabbed, true));  // fewest slots
     auto tables = [](const std::vector<TileOp>& v) {
         size_t c = 0;
         for (const TileOp& o : v) c += o.kind == CL_DIAG;
         return c;
     };
-    ops = tables(regrouped) < tables(runs) ? std::move(regrouped) : std::move(runs);
+    std::vector<TileOp>* best = &runs;
+    if (tables(late) < tables(*best)) best = &late;
+    if (tables(stabbed) < tables(*best)) best = &stabbed;
+    ops = std::move(*best);
     return QSV_OK;
 }
 
@@ -2124,7 +2192,10 @@ static thread_local FILE* g_plan_dump = nullptr;
 
 int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
     const bool no_fusion = flags & QSV_FLAG_NO_FUSION;
-    if (!no_fusion) fuse_gates(gates, s->n_local);
+    if (!no_fusion) {
+        fuse_gates(gates, s->n_local);
+        split_complex_1q(gates);
+    }
     size_t start = 0;
     while (start < gates.size()) {
         size_t end = start;
