@@ -31,7 +31,7 @@
 #define FP_MAX_DIAGS 40  // diagonal ops per pass
 #define FP_NOCOEF 0xffffffffu
 
-enum { FP_D1C = 0, FP_D1R = 1, FP_D2C = 2, FP_D2R = 3, FP_DIAG = 4, FP_DIAGU = 5 };
+enum { FP_D1C = 0, FP_D1R = 1, FP_D2C = 2, FP_D2R = 3, FP_DIAG = 4, FP_DIAGU = 5, FP_D1L = 6 };
 
 struct FpPhase {           // 80 bytes
     uint16_t rd[16];       // register r is read from byte offset (thread offset ^ rd[r]) of the tile buffer
@@ -132,6 +132,26 @@ __device__ __forceinline__ void fp_d1r(double2 (&v)[16], const FpPass& P, int mo
     }
 }
 
+// plane rotation (c -s ; s c), c >= 0, as three shears (lifting): x += t y; y += s x; x += t y with
+// t = -s / (1 + c) -- 3 FMA per real pair instead of 4 operations; |t| <= 1, so no amplification
+template <int B>
+__device__ __forceinline__ void fp_d1l(double2 (&v)[16], const FpPass& P, int mo) {
+    const double t = P.mats[mo + 0], s = P.mats[mo + 1];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        if (i & (1 << B)) continue;
+        double2 a0 = v[i], a1 = v[i | (1 << B)];
+        a0.x = fma(t, a1.x, a0.x);
+        a0.y = fma(t, a1.y, a0.y);
+        a1.x = fma(s, a0.x, a1.x);
+        a1.y = fma(s, a0.y, a1.y);
+        a0.x = fma(t, a1.x, a0.x);
+        a0.y = fma(t, a1.y, a0.y);
+        v[i] = a0;
+        v[i | (1 << B)] = a1;
+    }
+}
+
 template <int B0, int B1>
 __device__ __forceinline__ void fp_d2c(double2 (&v)[16], const FpPass& P, int mo) {
 #pragma unroll
@@ -221,6 +241,10 @@ __device__ __forceinline__ void fp_apply(double2 (&v)[16], const FpPass& P, int 
         case FP_D1R * 16 + 1: fp_d1r<1>(v, P, mo); break;
         case FP_D1R * 16 + 2: fp_d1r<2>(v, P, mo); break;
         case FP_D1R * 16 + 3: fp_d1r<3>(v, P, mo); break;
+        case FP_D1L * 16 + 0: fp_d1l<0>(v, P, mo); break;
+        case FP_D1L * 16 + 1: fp_d1l<1>(v, P, mo); break;
+        case FP_D1L * 16 + 2: fp_d1l<2>(v, P, mo); break;
+        case FP_D1L * 16 + 3: fp_d1l<3>(v, P, mo); break;
         case FP_D2C * 16 + 4: fp_d2c<0, 1>(v, P, mo); break;
         case FP_D2C * 16 + 8: fp_d2c<0, 2>(v, P, mo); break;
         case FP_D2C * 16 + 12: fp_d2c<0, 3>(v, P, mo); break;

@@ -1604,6 +1604,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
     uint64_t active = plan.qmask;
     for (int b = 0; b < n && popc64(active) < FP_T; ++b) active |= 1ull << b;  // low bits first
     if (popc64(active) != FP_T) return QSV_OK;
+    static const bool use_lifting = !getenv("QSV_NO_LIFT");
     FpPass& P = out.P;
     memset(&P, 0, sizeof P);
     int local_of[64];
@@ -2030,6 +2031,19 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
                 sb.kind = op.k == 1 ? (real ? FP_D1R : FP_D1C) : (real ? FP_D2R : FP_D2C);
                 sb.b = op.k == 1 ? (uint8_t)rb[0] : (uint8_t)(rb[order[0]] | (rb[order[1]] << 2));
                 sb.mat = (uint16_t)nmat;
+                if (op.k == 1 && real && use_lifting) {
+                    // a plane rotation (c -s ; s c) with c >= 0 (every RY, the real part of a split
+                    // RX / U3) runs as three shears: 3 instead of 4 FP64 operations per amplitude
+                    const double c = op.m[0].real(), ms = op.m[1].real(), sn = op.m[2].real(), c1 = op.m[3].real();
+                    if (c == c1 && ms == -sn && c >= 0.0 && std::abs(c * c + sn * sn - 1.0) < 1e-14) {
+                        sb.kind = FP_D1L;
+                        P.mats[nmat++] = -sn / (1.0 + c);
+                        P.mats[nmat++] = sn;
+                        ++nsubs;
+                        ++cnt;
+                        continue;
+                    }
+                }
                 for (int rc = 0; rc < dim; ++rc)
                     for (int cc = 0; cc < dim; ++cc) {
                         const cplx v = op.m[(size_t)to_orig(rc) * dim + to_orig(cc)];
@@ -2095,7 +2109,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
 }
 
 static void trace_fused_pass(const FpPass& P, FILE* f) {
-    int cnt[6] = {0, 0, 0, 0, 0, 0};
+    int cnt[7] = {0, 0, 0, 0, 0, 0, 0};
     fprintf(f, "[fused] T bits:");
     for (int b = 0; b < FP_T; ++b) fprintf(f, " %d", P.pos[b]);
     fprintf(f, " | %sphases %d:", P.warp_local ? "warp-local " : "", P.nphases);
@@ -2104,7 +2118,7 @@ static void trace_fused_pass(const FpPass& P, FILE* f) {
                 P.phases[p].rcoef != FP_NOCOEF ? "r" : "", P.phases[p].wcoef != FP_NOCOEF ? "w" : "");
         for (int i = 0; i < P.phases[p].nsub; ++i) cnt[P.subs[P.phases[p].sub_first + i].kind]++;
     }
-    fprintf(f, " | d1c %d d1r %d d2c %d d2r %d diag %d diagu %d | tabs %d\n", cnt[0], cnt[1], cnt[2], cnt[3], cnt[4], cnt[5],
+    fprintf(f, " | d1c %d d1r %d d1l %d d2c %d d2r %d diag %d diagu %d | tabs %d\n", cnt[0], cnt[1], cnt[6], cnt[2], cnt[3], cnt[4], cnt[5],
             P.ntabs);
 }
 
