@@ -405,8 +405,13 @@ class SamplerPub:
         vals = _bindings_array(pub[1] if len(pub) > 1 else None, circuit)
         if len(pub) > 2 and pub[2] is not None:
             shots = pub[2]
-        if shots is None or int(shots) != shots or shots < 0:
-            raise ValueError("shots must be a non-negative integer")
+        # sampler_pub.py:96-102, 149-153
+        from numbers import Integral
+
+        if shots is None or not isinstance(shots, Integral) or isinstance(shots, bool):
+            raise TypeError("shots must be an integer")
+        if shots <= 0:
+            raise ValueError("shots must be positive")
         return cls(circuit, vals, int(shots))
 
 

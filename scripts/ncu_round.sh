@@ -1,0 +1,11 @@
+# Round profile: (1) plain bench, (2) ncu launch list of the same command, (3) --set full over one SU2 evaluation's
+# fused passes, (4) --set full over the expval kernels.  Numbers printed under ncu are never bench values.
+O=gpurun_out/${1:-ncu_r1n}; mkdir -p $O
+timeout 600 python bench.py --steps 2 --warmup 3 > $O/bench_plain.json 2> $O/bench_plain.err; echo "plain bench exit $?"
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches_bench.csv \
+  python bench.py --steps 2 --warmup 3 > $O/bench_under_ncu.log 2>&1; echo "ncu launch list exit $?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_fused_pass -s 12 -c 12 \
+  -o $O/su2_fused -f python scripts/profile_run.py su2 > $O/ncu_su2.log 2>&1; echo "ncu fused exit $?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_expval -s 3 -c 3 \
+  -o $O/su2_expval -f python scripts/profile_run.py su2 > $O/ncu_expval.log 2>&1; echo "ncu expval exit $?"
+ls -la $O

@@ -13,7 +13,7 @@ import pytest
 
 from oracle import gate_matrices as ogm
 from oracle import statevector_ref as ref
-from qiskit_b200 import (Pauli, QiskitError, QuantumCircuit, SparsePauliOp, Statevector,
+from qiskit_b200 import (Pauli, PauliList, QiskitError, QuantumCircuit, SparsePauliOp, Statevector,
                          StatevectorEstimator, StatevectorSampler, ClassicalRegister, Parameter)
 from qiskit_b200 import circuit_library as lib
 from qiskit_b200.gates import gate_matrix
@@ -615,3 +615,45 @@ def test_sampler_errors_and_no_cregs():
     with pytest.warns(UserWarning):
         res = StatevectorSampler().run([bare], shots=10).result()
     assert len(res[0].data) == 0
+
+
+def test_edge_cases_small_and_empty():
+    """Empty / minimal inputs behave like the reference: 0- and 1-qubit states, empty qargs, zero
+    shots at the state level, empty operators, empty pub lists, invalid shots."""
+    sv1 = Statevector.from_int(0, 2)
+    np.testing.assert_array_equal(sv1.probabilities(), [1.0, 0.0])
+    np.testing.assert_array_equal(sv1.probabilities([]), [1.0])          # everything marginalised
+    assert sv1.sample_indices(0).shape == (0,) and sv1.sample_memory(0).shape == (0,)
+    assert sv1.sample_counts(5) == {"0": 5}
+    np.testing.assert_array_equal(Statevector(np.array([1.0 + 0j])).data, [1.0])   # zero qubits
+    np.testing.assert_array_equal(sv1.apply_gate_list([]).data, [1.0, 0.0])
+    empty = SparsePauliOp(PauliList(np.zeros((0, 1), bool), np.zeros((0, 1), bool)), np.zeros(0))
+    assert sv1.expectation_value(empty) == 0
+    assert sv1.expectation_value(Pauli("I")) == 1.0
+    plus = Statevector.from_label("+")
+    edge = np.array([0.0, 0.5, 1.0 - 2.0 ** -53])
+    np.testing.assert_array_equal(plus.sample_indices(3, uniforms=edge),
+                                  ref.tree_choice_indices(ref.tree_probabilities(plus.data), edge))
+    with pytest.raises(ValueError, match="do not sum to 1"):              # Generator.choice's check
+        Statevector(np.array([1.0, 1.0])).sample_indices(4)
+    with pytest.raises(QiskitError):
+        sv1.evolve(np.eye(2), [3])
+    with pytest.raises(QiskitError):
+        Statevector.from_int(0, 8).probabilities([1, 1])
+    assert len(StatevectorEstimator().run([]).result()) == 0
+    qc = QuantumCircuit(2)
+    qc.h(0)
+    qc.cx(0, 1)
+    np.testing.assert_allclose(StatevectorEstimator().run([(qc, ["ZZ", "XX", "YY", "II"])]).result()[0].data.evs,
+                               [1, 1, -1, 1], atol=ATOL)
+    with pytest.raises(ValueError):
+        StatevectorEstimator().run([(qc, "ZZZ")]).result()
+    qm = QuantumCircuit(2)
+    qm.h(0)
+    qm.cx(0, 1)
+    qm.measure_all()
+    with pytest.raises(ValueError, match="positive"):                     # sampler_pub.py:152-153
+        StatevectorSampler().run([qm], shots=0).result()
+    with pytest.raises(TypeError):
+        StatevectorSampler().run([qm], shots=1.5).result()
+    assert sum(StatevectorSampler(seed=1).run([qm], shots=1).result()[0].data.meas.get_counts().values()) == 1
