@@ -64,7 +64,8 @@ __device__ __forceinline__ void warp_block_prefix(const ProbSource& src, uint64_
 // totals[blk] = w[31][31] of block blk; optionally also the full in-block prefix w
 __global__ void __launch_bounds__(32 * WARPS_PER_CTA) k_block_totals(ProbSource src, uint64_t nblocks,
                                                                      double* __restrict__ totals,
-                                                                     double* __restrict__ w_out) {
+                                                                     double* __restrict__ w_out,
+                                                                     double* __restrict__ seg_out) {
     __shared__ double sm[WARPS_PER_CTA][SEG * PAD];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (uint64_t blk = blockIdx.x * (uint64_t)WARPS_PER_CTA + warp; blk < nblocks;
@@ -72,6 +73,8 @@ __global__ void __launch_bounds__(32 * WARPS_PER_CTA) k_block_totals(ProbSource 
         double s[SEG], E;
         warp_block_prefix(src, blk, sm[warp], s, E);
         if (lane == 31) totals[blk] = __dadd_rn(E, s[SEG - 1]);
+        // w[lane][31] of every segment (level 0): lets the search skip 31 of the block's 32 segments
+        if (seg_out) seg_out[blk * SEG + lane] = __dadd_rn(E, s[SEG - 1]);
         if (w_out) {
 #pragma unroll
             for (int k = 0; k < SEG; ++k) w_out[blk * BLK + (uint64_t)lane * SEG + k] = __dadd_rn(E, s[k]);
@@ -90,6 +93,7 @@ struct LevelDesc {
 #define MAX_SHARDS 16
 struct SearchParams {
     ProbSource src;  // level 0
+    const double* seg_w;  // level 0: w[seg][31] of every block (nullptr: recompute whole blocks)
     int nlevels;     // total number of levels including level 0
     LevelDesc lv[MAX_LEVELS];  // lv[k] for k >= 1
     double total;
@@ -139,6 +143,38 @@ __global__ void __launch_bounds__(32 * WARPS_PER_CTA) k_search(SearchParams P, c
             if (j > last) j = last;
             if (j > 0) X = __dadd_rn(X, w[j - 1]);
             blk = base + j;
+        }
+        if (P.seg_w) {
+            // level 0 through the stored segment ends: w[l][31] = fl(E_l + t_l) is both the value the
+            // full scan compares for item (l, 31) and E_{l+1}; items are non-decreasing, so the first
+            // segment whose end exceeds u holds the answer and only its 32 items are re-derived
+            const uint64_t base = blk * BLK;
+            uint64_t nv = P.src.count - base;
+            const int last = (int)(nv < BLK ? nv : BLK) - 1;
+            const double wl = P.seg_w[blk * SEG + lane];
+            const bool hit = __ddiv_rn(__dadd_rn(X, wl), P.total) > u;
+            const unsigned m = __ballot_sync(0xffffffffu, hit);
+            int j = BLK - 1;
+            if (m) {
+                const int l = __ffs(m) - 1;
+                const double prev = __shfl_sync(0xffffffffu, wl, l > 0 ? l - 1 : 0);
+                const double E = l > 0 ? prev : 0.0;
+                const double pk = prob_at(P.src, base + (uint64_t)l * SEG + lane);
+                double run = 0.0;
+#pragma unroll
+                for (int i = 0; i < SEG; ++i) {  // sequential in-segment prefix: lane k ends with s[k]
+                    const double v = __shfl_sync(0xffffffffu, pk, i);
+                    if (i == 0) run = v;
+                    else if (i <= lane) run = __dadd_rn(run, v);
+                }
+                const bool h2 = __ddiv_rn(__dadd_rn(X, __dadd_rn(E, run)), P.total) > u;
+                const unsigned m2 = __ballot_sync(0xffffffffu, h2);
+                j = l * SEG + (m2 ? __ffs(m2) - 1 : SEG - 1);
+            }
+            if (j > last) j = last;
+            if (lane == 0) out[sh] = (base + j) | P.index_base;
+            __syncwarp();
+            continue;
         }
         // level 0: recompute the in-block prefix from the source
         double s[SEG], E;
@@ -380,6 +416,10 @@ extern "C" int qsv_sample(const qsv_state* cs, const int* qargs, int m, const do
     size_t o_tot[MAX_LEVELS + 1], o_w[MAX_LEVELS + 1];
     for (int k = 0; k < nlevels; ++k) o_tot[k] = take(nblk[k] * sizeof(double));  // totals of level-k blocks
     for (int k = 1; k < nlevels; ++k) o_w[k] = take(nblk[k] * BLK * sizeof(double));
+    // stored segment ends of level 0 (1/32 of the items): worth it once the shots would otherwise
+    // re-read more than the extra array costs to write
+    const bool use_seg = shots >= 4096 && nblk[0] * SEG * sizeof(double) <= ((size_t)4 << 30);
+    size_t o_seg = use_seg ? take(nblk[0] * SEG * sizeof(double)) : 0;
     size_t o_all = take(MAX_SHARDS * sizeof(double));
     size_t o_u = take(shots * sizeof(double));
     size_t o_idx = take(shots * sizeof(uint64_t));
@@ -398,13 +438,15 @@ extern "C" int qsv_sample(const qsv_state* cs, const int* qargs, int m, const do
         uint64_t ctas = (nblk[0] + WARPS_PER_CTA - 1) / WARPS_PER_CTA;
         uint64_t cap = (uint64_t)s->num_sms * 8;
         if (ctas > cap) ctas = cap;
-        k_block_totals<<<(unsigned)ctas, threads, 0, s->stream>>>(src, nblk[0], (double*)(base + o_tot[0]), nullptr);
+        k_block_totals<<<(unsigned)ctas, threads, 0, s->stream>>>(src, nblk[0], (double*)(base + o_tot[0]), nullptr,
+                                                                  use_seg ? (double*)(base + o_seg) : nullptr);
         s->ctr.kernel_launches++;
         s->ctr.read_passes++;
     }
     SearchParams P;
     memset(&P, 0, sizeof P);
     P.src = src;
+    P.seg_w = use_seg ? (const double*)(base + o_seg) : nullptr;
     P.nlevels = nlevels;
     for (int k = 1; k < nlevels; ++k) {
         ProbSource lsrc;
@@ -413,7 +455,7 @@ extern "C" int qsv_sample(const qsv_state* cs, const int* qargs, int m, const do
         lsrc.count = nblk[k - 1];
         uint64_t ctas = (nblk[k] + WARPS_PER_CTA - 1) / WARPS_PER_CTA;
         k_block_totals<<<(unsigned)ctas, threads, 0, s->stream>>>(lsrc, nblk[k], (double*)(base + o_tot[k]),
-                                                                  (double*)(base + o_w[k]));
+                                                                  (double*)(base + o_w[k]), nullptr);
         s->ctr.kernel_launches++;
         P.lv[k].w = (const double*)(base + o_w[k]);
         P.lv[k].n_valid = nblk[k - 1];

@@ -411,6 +411,14 @@ def test_sample_edge_uniforms_and_sparse_states():
     want = ref.tree_choice_indices(ref.tree_probabilities(psi), u)
     assert np.array_equal(got, want) and set(got.tolist()) <= {5, 4000}
     assert Statevector(psi).sample_indices(0, uniforms=np.zeros(0)).size == 0
+    # the two level-0 search paths (stored segment ends for >= 4096 shots, whole-block rescan below)
+    # are the same arithmetic: identical indices for identical uniforms, also on a sparse state
+    for vec in (psi, random_state(15, 9)):
+        sv = Statevector(vec)
+        uu = np.random.default_rng(5).random(6000)
+        whole = sv.sample_indices(len(uu), uniforms=uu)
+        parts = np.concatenate([sv.sample_indices(3000, uniforms=uu[:3000]), sv.sample_indices(3000, uniforms=uu[3000:])])
+        assert np.array_equal(whole, parts)
 
 
 @pytest.mark.parametrize("n,qargs", [(6, [0, 3]), (12, [11, 2, 7]), (14, list(range(1, 14))), (13, [4])])
