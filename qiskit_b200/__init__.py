@@ -15,11 +15,12 @@ from .densitymatrix import DensityMatrix
 from .primitives import BitArray, StatevectorEstimator, StatevectorSampler
 from .basic_simulator import BasicSimulator
 from .sampled_expval import sampled_expectation_value
+from .backend_primitives import BackendEstimatorV2, BackendSamplerV2
 
 __all__ = [
     "QiskitError", "QuantumCircuit", "ClassicalRegister", "Parameter", "ParameterVector", "Gate",
     "Instruction", "Pauli", "PauliList", "SparsePauliOp", "Statevector", "DensityMatrix", "StatevectorEstimator",
-    "StatevectorSampler", "BitArray", "BasicSimulator", "sampled_expectation_value", "install",
+    "StatevectorSampler", "BitArray", "BasicSimulator", "BackendEstimatorV2", "BackendSamplerV2", "sampled_expectation_value", "install",
 ]
 __version__ = "0.1.0"
 
