@@ -86,6 +86,10 @@ struct qsv_state {
     // qsv_apply_gates, which then never has to read the zeros
     // out-of-place request: the next pass reads its tiles from this buffer instead of `amp`
     const double2* read_from;
+    // basis-change expectation values: the caller only needs |a|^2 of the result, so the last fused
+    // pass of the next qsv_apply_hgates may store probabilities (FpPass.store_prob).  prob_layout
+    // reports whether it did; the buffer then holds no amplitudes until it is rewritten.
+    int prob_store_req, prob_layout;
     int basis_pending;
     int lazy_init;  // option: 0 = qsv_init_basis writes the buffer immediately
     int use_product_init;  // option: product-state prologue in qsv_apply_gates

@@ -107,6 +107,9 @@ __global__ void __launch_bounds__(EV_THREADS) k_expval_batch(const double2* __re
 #define WHT_TERMS (WHT_JJ * 32)
 #define WHT_WARPS 8
 
+// PROB: the buffer holds |a|^2 in the layout k_fused_pass's store_prob leaves behind (probability
+// of amplitude i at double (i >> 4) * 32 + (i & 15)): half the bytes of the amplitude read.
+template <bool PROB>
 __global__ void __launch_bounds__(32 * WHT_WARPS) k_expval_z_wht(const double2* __restrict__ amp,
                                                                  uint64_t nchunks, uint64_t chunk_base,
                                                                  const uint64_t* __restrict__ zmasks,
@@ -124,12 +127,18 @@ __global__ void __launch_bounds__(32 * WHT_WARPS) k_expval_z_wht(const double2* 
     }
     for (uint64_t chunk = blockIdx.x * (uint64_t)WHT_WARPS + warp; chunk < nchunks;
          chunk += (uint64_t)gridDim.x * WHT_WARPS) {
-        const double2* src = amp + chunk * 256 + lane;
         double p[8];
+        if (PROB) {
+            const double* src = reinterpret_cast<const double*>(amp) + chunk * 512 + (lane & 15) + ((lane >> 4) << 5);
 #pragma unroll
-        for (int r = 0; r < 8; ++r) {
-            const double2 a = src[r * 32];
-            p[r] = a.x * a.x + a.y * a.y;
+            for (int r = 0; r < 8; ++r) p[r] = src[r * 64];
+        } else {
+            const double2* src = amp + chunk * 256 + lane;
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                const double2 a = src[r * 32];
+                p[r] = a.x * a.x + a.y * a.y;
+            }
         }
 #pragma unroll
         for (int sft = 1; sft < 8; sft <<= 1) {
@@ -256,7 +265,7 @@ struct TermItem {
 
 // Z-type terms of `st` (masks in zlist) -> d_res[slot0 ...]; one WHT pass per WHT_TERMS terms.
 static int run_wht_terms(qsv_state* st, const std::vector<uint64_t>& zlist, double* d_res,
-                         qsv_counters* ctr) {
+                         qsv_counters* ctr, bool prob_layout = false) {
     const uint64_t count = qsv_local_size(st);
     const uint64_t nchunks = count >> 8;
     const uint64_t chunk_base = st->world > 1 ? ((uint64_t)st->rank << (st->n_local - 8)) : 0;
@@ -275,8 +284,12 @@ static int run_wht_terms(qsv_state* st, const std::vector<uint64_t>& zlist, doub
         // pageable source: the copy is staged by the runtime before the call returns
         QSV_CUDA(cudaMemcpyAsync(d_z, zlist.data() + p0, nt * sizeof(uint64_t), cudaMemcpyHostToDevice,
                                  st->stream));
-        k_expval_z_wht<<<blocks, 32 * WHT_WARPS, 0, st->stream>>>(st->amp, nchunks, chunk_base, d_z, nt,
-                                                                  d_part, blocks);
+        if (prob_layout)
+            k_expval_z_wht<true><<<blocks, 32 * WHT_WARPS, 0, st->stream>>>(st->amp, nchunks, chunk_base, d_z, nt,
+                                                                            d_part, blocks);
+        else
+            k_expval_z_wht<false><<<blocks, 32 * WHT_WARPS, 0, st->stream>>>(st->amp, nchunks, chunk_base, d_z, nt,
+                                                                             d_part, blocks);
         k_reduce_partials<<<nt, EV_THREADS, 0, st->stream>>>(d_part, blocks, blocks, d_res + p0);
         QSV_CUDA(cudaGetLastError());
         ctr->kernel_launches += 2;
@@ -453,7 +466,32 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
         uint64_t cur_x = 0, cur_z = 0;
         bool have_copy = false;
         const double r2 = 0.70710678118654752440;
-        for (QwcGroup* g : rotated) {
+        // Which families start again from the state itself is decided up front: the family before
+        // such a restart (and the last one) leaves nothing anyone reads but |a|^2, so its final
+        // rotation pass stores probabilities only -- half the bytes written, half the bytes the
+        // Walsh-Hadamard pass reads.
+        static const bool prob_store = getenv("QSV_NO_PROB_STORE") == nullptr;
+        auto frame_at = [](uint64_t xb, uint64_t zb, uint64_t b) { return (xb & b) ? ((zb & b) ? 2 : 1) : 0; };
+        auto passes_needed = [](int nq) { return nq <= 0 ? 0 : (nq <= 12 ? 1 : 1 + (nq - 12 + 7) / 8); };
+        std::vector<char> restart(rotated.size(), 0);
+        {
+            uint64_t fx = 0, fz = 0;
+            for (size_t gi = 0; gi < rotated.size(); ++gi) {
+                int n_cur = 0, n_psi = 0;
+                for (int q = 0; q < s->n_local; ++q) {
+                    const uint64_t b = 1ull << q;
+                    const int want = frame_at(rotated[gi]->xb, rotated[gi]->zb, b);
+                    n_cur += want != frame_at(fx, fz, b);
+                    n_psi += want != 0;
+                }
+                restart[gi] = gi == 0 || passes_needed(n_psi) <= passes_needed(n_cur);
+                fx = rotated[gi]->xb;  // every local qubit ends in the family's frame (Z where it has no X)
+                fz = rotated[gi]->zb & rotated[gi]->xb;
+            }
+        }
+        for (size_t gi = 0; gi < rotated.size(); ++gi) {
+            QwcGroup* g = rotated[gi];
+            const bool last_use = gi + 1 == rotated.size() || restart[gi + 1];
             // Two ways to reach this family's frame: keep rotating the scratch copy in place, or start
             // again from the state itself (out of place, no copy).  From the Z frame every rotation is
             // a real H, preceded by a diagonal S^dagger for Y -- half the FP64 work of the complex
@@ -467,7 +505,7 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
                 n_psi += want != 0;
             }
             auto passes_for = [](int nq) { return nq <= 0 ? 0 : (nq <= 12 ? 1 : 1 + (nq - 12 + 7) / 8); };
-            if (!have_copy || passes_for(n_psi) <= passes_for(n_cur)) {
+            if (!have_copy || restart[gi]) {
                 // no copy: the first rotation pass reads the state and writes the scratch buffer
                 aux->read_from = s->amp;
                 have_copy = true;
@@ -517,6 +555,7 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
             }
             if (!layer.empty()) {
                 const uint64_t before_l = aux->ctr.kernel_launches, before_p = aux->ctr.state_passes;
+                aux->prob_store_req = prob_store && last_use;
                 QSV_TRY(qsv_apply_hgates(aux, layer, 0));
                 s->ctr.kernel_launches += aux->ctr.kernel_launches - before_l;
                 s->ctr.state_passes += aux->ctr.state_passes - before_p;
@@ -531,7 +570,12 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
                 const int d = ((it.sel - it.ny) % 4 + 4) % 4;
                 factor[it.idx] = d == 0 ? 1.0 : (d == 2 ? -1.0 : 0.0);
             }
-            QSV_TRY(run_wht_terms(aux, zl, d_res + slot, &s->ctr));
+            const bool probs = !layer.empty() && aux->prob_layout;
+            QSV_TRY(run_wht_terms(aux, zl, d_res + slot, &s->ctr, probs));
+            if (probs) {
+                aux->prob_layout = 0;
+                have_copy = false;  // the buffer holds no amplitudes any more
+            }
             // run_wht_terms wrote through aux's scratch into this handle's d_res: same stream
             slot += g->members.size();
         }

@@ -69,6 +69,8 @@ struct FpPass {
     int32_t nphases;
     int32_t ntabs;
     int32_t warp_local;    // phases exchange data inside warps only (__syncwarp between phases)
+    int32_t store_prob;    // direct-store last phase writes |a|^2 only: amplitude i -> double (i >> 4) * 32 + (i & 15),
+                           // i.e. the first half of the 256-byte run the tile itself owns (in place, no hazard)
     int32_t pos[FP_T];     // ascending global bit position of tile bit b
     const uint16_t* tabs;  // [ntabs][256]
     const double2* gdata;  // diagonal tables and coefficient vectors
@@ -347,8 +349,16 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const dou
             }
             if (ph.direct) {
                 char* g = reinterpret_cast<char*>(amp + tile_base + st_thread);
+                if (P.store_prob) {
+                    g -= (st_thread & 15ull) << 3;
 #pragma unroll
-                for (int r = 0; r < 16; ++r) *reinterpret_cast<double2*>(g + P.st_off[r]) = v[r];
+                    for (int r = 0; r < 16; ++r)
+                        *reinterpret_cast<double*>(g + P.st_off[r] - (((P.st_off[r] >> 4) & 15ull) << 3)) =
+                            v[r].x * v[r].x + v[r].y * v[r].y;
+                } else {
+#pragma unroll
+                    for (int r = 0; r < 16; ++r) *reinterpret_cast<double2*>(g + P.st_off[r]) = v[r];
+                }
                 stored = true;
             } else {
 #pragma unroll

@@ -2206,6 +2206,9 @@ static thread_local FILE* g_plan_dump = nullptr;
 
 int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
     const bool no_fusion = flags & QSV_FLAG_NO_FUSION;
+    const bool want_prob = s->prob_store_req != 0;  // one-shot request (qsv_expval.cu)
+    s->prob_store_req = 0;
+    s->prob_layout = 0;
     if (!no_fusion) {
         fuse_gates(gates, s->n_local);
         split_complex_1q(gates);
@@ -2275,6 +2278,13 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
                                          s->stream));
                 s->ctr.state_passes++;
                 s->read_from = nullptr;
+            }
+            if (want_prob && end == gates.size() && !passes.empty() && kind.back() == 3 && !s->use_fused3) {
+                FpPass& last = fparams.back().P;
+                if (last.nphases > 0 && last.phases[last.nphases - 1].direct) {
+                    last.store_prob = 1;
+                    s->prob_layout = 1;
+                }
             }
             for (size_t i = 0; i < passes.size(); ++i) {
                 char* base = (char*)s->scratch;
