@@ -90,9 +90,17 @@ struct qsv_state {
     // pass of the next qsv_apply_hgates may store probabilities (FpPass.store_prob).  prob_layout
     // reports whether it did; the buffer then holds no amplitudes until it is rewritten.
     int prob_store_req, prob_layout;
+    // product-state prologue (qsv_gate.cu): the half-register tables stay here until the first fused
+    // pass generates its tiles from them (prod_pending) -- the state is then never written and read
+    // back before its first gates; any other consumer calls qsv_flush_product first
+    double2* prod_tab;
+    size_t prod_tab_bytes;
+    int prod_pending, prod_h;
+    double prod_vec[64][4];  // per qubit: (re, im) of the amplitudes of |0> and |1>
     int basis_pending;
     int lazy_init;  // option: 0 = qsv_init_basis writes the buffer immediately
     int use_product_init;  // option: product-state prologue in qsv_apply_gates
+    int use_product_fold;  // option: the first fused pass generates its tiles from the product tables
     uint64_t basis_index;
 };
 
@@ -112,6 +120,7 @@ struct HGate {
 int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags);
 
 int qsv_materialize(qsv_state* s);  // write a pending |index> into the amplitude buffer
+int qsv_flush_product(qsv_state* s);  // write a pending product state into the amplitude buffer (qsv_gate.cu)
 int qsv_ensure_scratch(qsv_state* s, size_t bytes);
 int qsv_ensure_pinned(qsv_state* s, size_t bytes);
 

@@ -237,6 +237,7 @@ extern "C" int qsv_permute_qubits(qsv_state* dst, const qsv_state* csrc, const i
     QSV_TRY(qsv_materialize(src));
     QSV_CUDA(cudaStreamSynchronize(src->stream));
     dst->basis_pending = 0;
+    dst->prod_pending = 0;
     const uint64_t count = qsv_local_size(dst);
     k_permute_bits<<<dn_grid(dst, count), DN_THREADS, 0, dst->stream>>>(dst->amp, src->amp, count, dst->n, first_moved, M);
     QSV_CUDA(cudaGetLastError());
@@ -274,6 +275,7 @@ extern "C" int qsv_tensor(qsv_state* dst, const qsv_state* ca, const qsv_state* 
     QSV_CUDA(cudaStreamSynchronize(a->stream));
     QSV_CUDA(cudaStreamSynchronize(b->stream));
     dst->basis_pending = 0;
+    dst->prod_pending = 0;
     const uint64_t count = qsv_local_size(dst);
     k_tensor<<<dn_grid(dst, count), DN_THREADS, 0, dst->stream>>>(dst->amp, a->amp, b->amp, count, a->n, b->n, A, B, conj_b);
     QSV_CUDA(cudaGetLastError());

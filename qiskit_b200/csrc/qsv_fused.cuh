@@ -69,6 +69,15 @@ struct FpPass {
     int32_t nphases;
     int32_t ntabs;
     int32_t warp_local;    // phases exchange data inside warps only (__syncwarp between phases)
+    // gen_h > 0: product-state prologue folded into this (first) pass.  No tile is read: the state
+    // is a product over qubits, so every tile is the same 2^12 amplitudes (the product over the tile's
+    // qubits, gen_tile, in tile-index order) times one scalar,
+    //   gen_lo[base mod 2^gen_h] * gen_hi[base div 2^gen_h]  (qubits outside the tile; base = tile base).
+    // The copy-in streams gen_tile (64 KB, L2-resident) instead of the state; phase 0 applies the scalar.
+    int32_t gen_h;
+    const double2* gen_lo;
+    const double2* gen_hi;
+    const double2* gen_tile;
     int32_t store_prob;    // direct-store last phase writes |a|^2 only: amplitude i -> double (i >> 4) * 32 + (i & 15),
                            // i.e. the first half of the 256-byte run the tile itself owns (in place, no hazard)
     int32_t pos[FP_T];     // ascending global bit position of tile bit b
@@ -300,12 +309,21 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const dou
         return base;
     };
     auto issue_load = [&](uint64_t tile_base) {
-        const char* g = reinterpret_cast<const char*>(src + tile_base + cp_off);
         const uint32_t dst0 = (uint32_t)__cvta_generic_to_shared(tilebuf);
+        if (P.gen_h > 0) {
+            const char* g = reinterpret_cast<const char*>(P.gen_tile + t);
 #pragma unroll
-        for (int r = 0; r < 16; ++r) {
-            const uint32_t dst = dst0 + (st16 ^ (fp_swz((uint32_t)r << 8) << 4));
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(g + P.row_off[r]));
+            for (int r = 0; r < 16; ++r) {
+                const uint32_t dst = dst0 + (st16 ^ (fp_swz((uint32_t)r << 8) << 4));
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(g + r * (FP_NT * 16)));
+            }
+        } else {
+            const char* g = reinterpret_cast<const char*>(src + tile_base + cp_off);
+#pragma unroll
+            for (int r = 0; r < 16; ++r) {
+                const uint32_t dst = dst0 + (st16 ^ (fp_swz((uint32_t)r << 8) << 4));
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(g + P.row_off[r]));
+            }
         }
         asm volatile("cp.async.commit_group;\n" ::: "memory");
     };
@@ -321,14 +339,26 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const dou
         const bool has_next = next < P.ntiles;
         const uint64_t next_base = has_next ? tile_base_of(next) : 0;
         const uint64_t diag_base = tile_base | P.index_base;
+        if (P.gen_h > 0 && has_next) {  // the next tile's two table entries: into L1 ahead of their use
+            asm volatile("prefetch.global.L1 [%0];\n" ::"l"(P.gen_lo + (next_base & ((1ull << P.gen_h) - 1))));
+            asm volatile("prefetch.global.L1 [%0];\n" ::"l"(P.gen_hi + (next_base >> P.gen_h)));
+        }
         bool stored = false;
 #pragma unroll 1
         for (int p = 0; p < P.nphases; ++p) {
             const FpPhase& ph = P.phases[p];
             const uint32_t sb = (uint32_t)tabs_sm[ph.tab * FP_NT + t] << 4;
             double2 v[16];
+            if (P.gen_h > 0 && p == 0) {
+                const double2 cb = cmul(__ldg(P.gen_lo + (tile_base & ((1ull << P.gen_h) - 1))),
+                                        __ldg(P.gen_hi + (tile_base >> P.gen_h)));
 #pragma unroll
-            for (int r = 0; r < 16; ++r) v[r] = *reinterpret_cast<const double2*>(tilebuf + (sb ^ ph.rd[r]));
+                for (int r = 0; r < 16; ++r)
+                    v[r] = cmul(cb, *reinterpret_cast<const double2*>(tilebuf + (sb ^ ph.rd[r])));
+            } else {
+#pragma unroll
+                for (int r = 0; r < 16; ++r) v[r] = *reinterpret_cast<const double2*>(tilebuf + (sb ^ ph.rd[r]));
+            }
             if (ph.direct) {
                 // every thread has its registers: the buffer can take the next tile now
                 __syncthreads();

@@ -2122,7 +2122,10 @@ static void trace_fused_pass(const FpPass& P, FILE* f) {
             P.ntabs);
 }
 
-static int launch_fused_pass(qsv_state* s, const FpPass& P) {
+static int upload_product_tables(qsv_state* s, uint64_t neutral, const std::vector<cplx>& extra);
+
+static int launch_fused_pass(qsv_state* s, const FusedBuilt& fb) {
+    const FpPass& P = fb.P;
     const size_t smem = FP_TILE * sizeof(double2) + (size_t)P.ntabs * FP_NT * sizeof(uint16_t);
     static bool attr_set = false;
     if (!attr_set) {
@@ -2135,6 +2138,43 @@ static int launch_fused_pass(qsv_state* s, const FpPass& P) {
     if (trace) QSV_CUDA(cudaEventRecord(s->ev0, s->stream));
     const double2* src = s->read_from ? s->read_from : s->amp;
     s->read_from = nullptr;  // only the first pass after the request reads the other buffer
+    if (s->prod_pending && (s->use_fused3 || !s->use_product_fold)) QSV_TRY(qsv_flush_product(s));
+    if (s->prod_pending) {
+        // first pass after the product-state prologue: nothing is read, phase 0 builds its registers
+        // from the per-qubit vectors (FpPass.gen_*)
+        s->prod_pending = 0;
+        FpPass G = P;
+        uint64_t tile_qubits = 0;
+        for (int b = 0; b < FP_T; ++b) tile_qubits |= 1ull << P.pos[b];
+        std::vector<cplx> tmpl(FP_TILE);  // the tile every tile is a multiple of
+        for (uint32_t y = 0; y < FP_TILE; ++y) {
+            cplx v(1.0, 0.0);
+            for (int b = 0; b < FP_T; ++b) {
+                const double* pv = s->prod_vec[P.pos[b]];
+                v *= ((y >> b) & 1u) ? cplx(pv[2], pv[3]) : cplx(pv[0], pv[1]);
+            }
+            tmpl[y] = v;
+        }
+        QSV_TRY(upload_product_tables(s, tile_qubits, tmpl));
+        G.gen_h = s->prod_h;
+        G.gen_lo = s->prod_tab;
+        G.gen_hi = G.gen_lo + ((size_t)1 << s->prod_h);
+        G.gen_tile = G.gen_hi + ((size_t)1 << (s->n_local - s->prod_h));
+        unsigned grid = (unsigned)std::min<uint64_t>(G.ntiles, (uint64_t)s->num_sms * 2);
+        if (trace) fprintf(stderr, "        (product state: the copy-in streams the 64 KB template tile, no state read)\n");
+        k_fused_pass<<<grid, FP_NT, smem, s->stream>>>(s->amp, s->amp, G);
+        QSV_CUDA(cudaGetLastError());
+        if (trace) {
+            float ms = 0.f;
+            QSV_CUDA(cudaEventRecord(s->ev1, s->stream));
+            QSV_CUDA(cudaEventSynchronize(s->ev1));
+            QSV_CUDA(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+            fprintf(stderr, "        -> %.3f ms\n", ms);
+        }
+        s->ctr.kernel_launches++;
+        s->ctr.write_passes++;  // one sweep written, none read
+        return QSV_OK;
+    }
     if (s->use_fused3) {
         static bool attr3_set = false;
         const size_t tabs_max = FP_MAX_TABS * FP_NT * sizeof(uint16_t);
@@ -2273,6 +2313,7 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
                 QSV_CUDA(cudaMemcpyAsync(s->scratch, s->pinned, used, cudaMemcpyHostToDevice, s->stream));
                 s->ctr.h2d_bytes += used;
             }
+            if (!passes.empty() && kind[0] != 3) QSV_TRY(qsv_flush_product(s));
             if (s->read_from && kind[0] != 3) {  // out-of-place request, but the first pass cannot do it
                 QSV_CUDA(cudaMemcpyAsync(s->amp, s->read_from, (size_t)16 << s->n_local, cudaMemcpyDeviceToDevice,
                                          s->stream));
@@ -2293,7 +2334,7 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
                 } else if (kind[i] == 3) {
                     fparams[i].P.tabs = (const uint16_t*)(base + fparams[i].tabs_off);
                     fparams[i].P.gdata = (const double2*)(base + fparams[i].gdata_off);
-                    QSV_TRY(launch_fused_pass(s, fparams[i].P));
+                    QSV_TRY(launch_fused_pass(s, fparams[i]));
                 } else if (kind[i] == 1) {
                     cparams[i].phases = (const ClPhase*)(base + ops_off[i]);
                     cparams[i].subs = (const ClSub*)(base + subs_off[i]);
@@ -2307,6 +2348,7 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
             }
         }
         if (end < gates.size()) {
+            QSV_TRY(qsv_flush_product(s));
             if (s->read_from) {
                 QSV_CUDA(cudaMemcpyAsync(s->amp, s->read_from, (size_t)16 << s->n_local, cudaMemcpyDeviceToDevice,
                                          s->stream));
@@ -2387,42 +2429,79 @@ static int product_prologue(qsv_state* s, std::vector<HGate>& hg) {
         }
     }
     if (!count) return QSV_OK;
-    const int h = (n + 1) / 2;
-    const size_t nlo = (size_t)1 << h, nhi = (size_t)1 << (n - h);
-    const size_t bytes = (nlo + nhi) * sizeof(double2);
-    QSV_TRY(qsv_ensure_scratch(s, bytes + 256));
-    QSV_TRY(qsv_ensure_pinned(s, bytes + 256));
-    QSV_CUDA(cudaStreamSynchronize(s->stream));  // pinned staging reuse
-    cplx* tab = reinterpret_cast<cplx*>(s->pinned);
-    auto fill = [&](cplx* t, int q0, int nq) {  // t[i] = prod_j vec[q0 + j][bit j of i]
-        t[0] = 1.0;
-        for (int j = 0; j < nq; ++j) {
-            const size_t half = (size_t)1 << j;
-            for (size_t i = 0; i < half; ++i) {
-                t[i + half] = t[i] * vec[q0 + j][1];
-                t[i] = t[i] * vec[q0 + j][0];
-            }
-        }
-    };
-    fill(tab, 0, h);
-    fill(tab + nlo, h, n - h);
-    QSV_CUDA(cudaMemcpyAsync(s->scratch, s->pinned, bytes, cudaMemcpyHostToDevice, s->stream));
-    s->ctr.h2d_bytes += bytes;
-    const uint64_t total = qsv_local_size(s);
-    uint64_t blocks = (total + 255) / 256;
-    const uint64_t cap = (uint64_t)s->num_sms * 16;
-    if (blocks > cap) blocks = cap;
-    const double2* d_lo = reinterpret_cast<const double2*>(s->scratch);
-    k_product_state<<<(unsigned)blocks, 256, 0, s->stream>>>(s->amp, total, h, d_lo, d_lo + nlo);
-    QSV_CUDA(cudaGetLastError());
-    s->ctr.kernel_launches++;
-    s->ctr.write_passes++;
+    // the sweep is deferred: the first fused pass builds its registers from the per-qubit vectors
+    // (launch_fused_pass); whoever else touches the buffer first calls qsv_flush_product
+    for (int q = 0; q < n; ++q) {
+        s->prod_vec[q][0] = vec[q][0].real();
+        s->prod_vec[q][1] = vec[q][0].imag();
+        s->prod_vec[q][2] = vec[q][1].real();
+        s->prod_vec[q][3] = vec[q][1].imag();
+    }
+    s->prod_pending = 1;
     s->basis_pending = 0;
     std::vector<HGate> rest;
     rest.reserve(hg.size() - count);
     for (size_t i = 0; i < hg.size(); ++i)
         if (!consumed[i]) rest.push_back(std::move(hg[i]));
     hg.swap(rest);
+    return QSV_OK;
+}
+
+// Upload the half-register tables of the pending product state: lo[i] = prod_{q < h} vec[q][bit q of i],
+// hi likewise for the qubits from h up; qubits in `neutral` contribute the factor 1 (they are
+// supplied elsewhere).  `extra` complex numbers are appended after the two tables.
+static int upload_product_tables(qsv_state* s, uint64_t neutral, const std::vector<cplx>& extra) {
+    const int n = s->n_local;
+    const int h = (n + 1) / 2;
+    const size_t nlo = (size_t)1 << h, nhi = (size_t)1 << (n - h);
+    const size_t bytes = (nlo + nhi + extra.size()) * sizeof(double2);
+    if (s->prod_tab_bytes < bytes) {
+        if (s->prod_tab) QSV_CUDA(cudaFree(s->prod_tab));
+        s->prod_tab = nullptr;
+        s->prod_tab_bytes = 0;
+        QSV_CUDA(cudaMalloc(&s->prod_tab, bytes));
+        s->prod_tab_bytes = bytes;
+    }
+    std::vector<cplx> tab(nlo + nhi + extra.size());
+    auto fill = [&](cplx* t, int q0, int nq) {  // t[i] = prod_j vec[q0 + j][bit j of i]
+        t[0] = 1.0;
+        for (int j = 0; j < nq; ++j) {
+            const double* pv = s->prod_vec[q0 + j];
+            const bool skip = (neutral >> (q0 + j)) & 1ull;
+            const cplx v0 = skip ? cplx(1.0, 0.0) : cplx(pv[0], pv[1]);
+            const cplx v1 = skip ? cplx(1.0, 0.0) : cplx(pv[2], pv[3]);
+            const size_t half = (size_t)1 << j;
+            for (size_t i = 0; i < half; ++i) {
+                t[i + half] = t[i] * v1;
+                t[i] = t[i] * v0;
+            }
+        }
+    };
+    fill(tab.data(), 0, h);
+    fill(tab.data() + nlo, h, n - h);
+    std::copy(extra.begin(), extra.end(), tab.begin() + nlo + nhi);
+    // pageable source: staged by the runtime before the call returns (the pinned area may still be
+    // feeding the pass descriptors to the device)
+    QSV_CUDA(cudaMemcpyAsync(s->prod_tab, tab.data(), bytes, cudaMemcpyHostToDevice, s->stream));
+    s->ctr.h2d_bytes += bytes;
+    s->prod_h = h;
+    return QSV_OK;
+}
+
+int qsv_flush_product(qsv_state* s) {
+    if (!s->prod_pending) return QSV_OK;
+    s->prod_pending = 0;
+    QSV_TRY(upload_product_tables(s, 0, {}));
+    const uint64_t total = qsv_local_size(s);
+    uint64_t blocks = (total + 255) / 256;
+    const uint64_t cap = (uint64_t)s->num_sms * 16;
+    if (blocks > cap) blocks = cap;
+    const double2* d_lo = s->prod_tab;
+    k_product_state<<<(unsigned)blocks, 256, 0, s->stream>>>(s->amp, total, s->prod_h, d_lo,
+                                                             d_lo + ((size_t)1 << s->prod_h));
+    QSV_CUDA(cudaGetLastError());
+    s->ctr.kernel_launches++;
+    s->ctr.write_passes++;
     return QSV_OK;
 }
 
@@ -2476,11 +2555,14 @@ static int qsv_apply_gates_impl(qsv_state* s, const qsv_gate* gates, uint64_t n_
         // |index> is still only recorded: fold the leading one-qubit gates into a product state and
         // write it in one sweep (no zero fill, no read); otherwise write |index> now
         if (!(flags & QSV_FLAG_NO_FUSION) && s->use_product_init) QSV_TRY(product_prologue(s, hg));
-        QSV_TRY(qsv_materialize(s));
+        if (!s->prod_pending) QSV_TRY(qsv_materialize(s));
     }
+    if (hg.empty() || s->world > 1) QSV_TRY(qsv_flush_product(s));
     if (hg.empty()) return QSV_OK;
     if (s->world > 1) return qsv_dist_apply(s, hg, flags);
-    return qsv_apply_hgates(s, hg, flags);
+    const int rc = qsv_apply_hgates(s, hg, flags);
+    if (rc != QSV_OK) return rc;
+    return qsv_flush_product(s);  // no pass took it (cannot happen with a non-empty stream; cheap to guarantee)
 }
 
 // Host-only view of the single-GPU pass planner (no device work): writes one line per pass to

@@ -82,6 +82,7 @@ void qsv_state_defaults(qsv_state* s) {
     s->use_diag_split = env_int("QSV_DIAG_SPLIT", 1);
     s->lazy_init = env_int("QSV_LAZY_INIT", 1);
     s->use_product_init = env_int("QSV_PRODUCT_INIT", 1);
+    s->use_product_fold = env_int("QSV_PRODUCT_FOLD", 1);
     s->use_warp_local = env_int("QSV_WARP_LOCAL", 0);  // measured: no gain (barriers are not the limiter), and its 32-byte store segments cost 20 %
 }
 
@@ -156,6 +157,7 @@ extern "C" int qsv_destroy(qsv_state* s) {
     if (s->amp) cudaFree(s->amp);
     if (s->scratch) cudaFree(s->scratch);
     if (s->flush_buf) cudaFree(s->flush_buf);
+    if (s->prod_tab) cudaFree(s->prod_tab);
     if (s->pinned) cudaFreeHost(s->pinned);
     cudaEventDestroy(s->ev0);
     cudaEventDestroy(s->ev1);
@@ -182,6 +184,7 @@ extern "C" int qsv_clone(const qsv_state* s, qsv_state** out) {
     c->use_diag_split = s->use_diag_split;
     c->lazy_init = s->lazy_init;
     c->use_product_init = s->use_product_init;
+    c->use_product_fold = s->use_product_fold;
     QSV_TRY(qsv_materialize(const_cast<qsv_state*>(s)));
     c->basis_pending = 0;
     QSV_CUDA(cudaStreamSynchronize(s->stream));
@@ -199,6 +202,7 @@ extern "C" int qsv_copy_state(qsv_state* dst, const qsv_state* src) {
     QSV_CUDA(cudaSetDevice(src->device));
     QSV_TRY(qsv_materialize(const_cast<qsv_state*>(src)));
     dst->basis_pending = 0;
+    dst->prod_pending = 0;
     QSV_CUDA(cudaStreamSynchronize(src->stream));
     QSV_CUDA(cudaMemcpyAsync(dst->amp, src->amp, (size_t)16 << src->n_local, cudaMemcpyDeviceToDevice,
                              dst->stream));
@@ -229,6 +233,7 @@ static int write_basis(qsv_state* s, uint64_t index) {
 }
 
 int qsv_materialize(qsv_state* s) {
+    if (s->prod_pending) return qsv_flush_product(s);  // only after a failed qsv_apply_gates
     if (!s->basis_pending) return QSV_OK;
     s->basis_pending = 0;
     return write_basis(s, s->basis_index);
@@ -241,6 +246,7 @@ extern "C" int qsv_init_basis(qsv_state* s, uint64_t index) {
                  (unsigned long long)index, s->n);
     QSV_CUDA(cudaSetDevice(s->device));
     for (int q = 0; q < 64; ++q) s->perm[q] = q;
+    s->prod_pending = 0;
     if (s->world == 1 && s->lazy_init) {  // deferred: see qsv_state::basis_pending
         s->basis_pending = 1;
         s->basis_index = index;
@@ -259,7 +265,7 @@ extern "C" int qsv_upload(qsv_state* s, const double* c128, uint64_t offset, uin
                  (unsigned long long)offset, (unsigned long long)(offset + count),
                  (unsigned long long)qsv_local_size(s));
     QSV_CUDA(cudaSetDevice(s->device));
-    if (count == qsv_local_size(s)) s->basis_pending = 0;  // a full overwrite needs no zeros first
+    if (count == qsv_local_size(s)) s->basis_pending = s->prod_pending = 0;  // a full overwrite needs no zeros first
     QSV_TRY(qsv_materialize(s));
     if (s->world > 1) QSV_TRY(qsv_dist_canonicalize(s));
     QSV_CUDA(cudaMemcpyAsync(s->amp + offset, c128, count * 16, cudaMemcpyHostToDevice, s->stream));
@@ -347,6 +353,8 @@ extern "C" int qsv_set_option(qsv_state* s, const char* name, int64_t value) {
         s->use_diag_split = value != 0;
     } else if (!strcmp(name, "product_init")) {
         s->use_product_init = value != 0;
+    } else if (!strcmp(name, "product_fold")) {
+        s->use_product_fold = value != 0;
     } else if (!strcmp(name, "lazy_init")) {
         QSV_TRY(qsv_materialize(s));
         s->lazy_init = value != 0;
