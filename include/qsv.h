@@ -217,7 +217,14 @@ int qsv_reset_counters(qsv_state* s);
  * second one, synchronises and returns the elapsed milliseconds between them. */
 int qsv_timer_begin(qsv_state* s);
 int qsv_timer_end(qsv_state* s, float* ms_out);
-/* engine tunables, by name ("tile_bits", "low_bits", ...); for experiments */
+/* engine tunables, by name; for experiments and A/B measurements, the defaults are the product:
+ *   tile_bits, low_bits, tile_threads      tile geometry of the unfused tile pass
+ *   use_direct, use_cluster, use_fused     which kernel takes a pass (k_direct*, k_cluster_pass, k_fused_pass)
+ *   direct_store, warp_local, fused3, linear_perm, diag_split   k_fused_pass variants
+ *   lazy_init, product_init, product_fold  deferred |index>, product-state prologue, prologue folded
+ *                                          into the first fused pass
+ * Environment switches read once per process: QSV_TRACE (per-pass plan + time on stderr),
+ * QSV_NO_ZYZ, QSV_NO_LIFT (planner rewrites), QSV_NO_PROB_STORE (basis-change expval keeps amplitudes). */
 int qsv_set_option(qsv_state* s, const char* name, int64_t value);
 /* write a buffer larger than L2 (flush between timed iterations) */
 int qsv_flush_l2(qsv_state* s);

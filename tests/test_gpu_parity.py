@@ -152,9 +152,10 @@ def test_product_state_prologue_and_lazy_basis(n):
         named = random_named_circuit(n, 8 * n + 5, seed=n + start, names=names)
         gates = lib.named_to_matrices(named)
         want = ref.apply_gate_list(ref.basis_state(n, start), oracle_matrices(named))
-        for product_init in (1, 0):
+        for product_init, fold in ((1, 1), (1, 0), (0, 1)):
             sv = Statevector.from_int(start, 1 << n)
             sv.set_option("product_init", product_init)
+            sv.set_option("product_fold", fold)   # first fused pass streams the template tile / separate sweep
             w0 = sv.counters()["write_passes"]      # pooled handles keep cumulative counters
             sv.apply_gate_list(gates)
             assert np.max(np.abs(sv.data - want)) < ATOL, (n, start, product_init)
@@ -336,6 +337,32 @@ def test_expval_many_z_terms_and_qwc_families(n):
     assert abs(sv.expectation_value(op) - want) < ATOL
     assert sv.counters()["read_passes"] - before < len(labels) // 2     # batched, not per term
     np.testing.assert_array_equal(sv.data, psi)                          # the state is untouched
+
+
+def test_expval_families_continue_and_restart():
+    """Three rotated families on 20 qubits: X strings (2 passes from the state), the same with Y on
+    qubit 0 (1 pass continuing the rotated copy in place, so the first family must leave amplitudes
+    behind), all-Y strings (restart from the state, so the second family may leave |a|^2 only)."""
+    n = 20
+    rng = np.random.default_rng(20)
+    psi = random_state(n, 21)
+    sv = Statevector(psi)
+    labels = []
+    for first, other in (("X", "X"), ("Y", "X"), ("Y", "Y")):
+        for _ in range(14):
+            supp = rng.integers(2, size=n).astype(bool)
+            supp[0] = True
+            labels.append("".join((first if q == 0 else other) if supp[q] else "I" for q in reversed(range(n))))
+    labels = list(dict.fromkeys(labels))
+    op = SparsePauliOp(labels, rng.standard_normal(len(labels)))
+    want = ref.expectation_value_sparse(psi, op.paulis.z, op.paulis.x, op.coeffs)
+    before = sv.counters()
+    assert abs(sv.expectation_value(op) - want) < ATOL
+    after = sv.counters()
+    assert after["state_passes"] - before["state_passes"] == 5     # 2 + 1 + 2 rotation passes
+    assert after["read_passes"] - before["read_passes"] == 3
+    np.testing.assert_array_equal(sv.data, psi)
+    assert abs(sv.expectation_value(op) - want) < ATOL              # and again, from the reused scratch copy
 
 
 def test_expval_generic_operator_and_inner():
