@@ -109,20 +109,26 @@ __global__ void __launch_bounds__(EV_THREADS) k_expval_batch(const double2* __re
 
 // PROB: the buffer holds |a|^2 in the layout k_fused_pass's store_prob leaves behind (probability
 // of amplitude i at double (i >> 4) * 32 + (i & 15)): half the bytes of the amplitude read.
-template <bool PROB>
-__global__ void __launch_bounds__(32 * WHT_WARPS) k_expval_z_wht(const double2* __restrict__ amp,
+// JJ: terms per lane (the launch serves up to 32 * JJ terms); fewer terms -> fewer registers -> a
+// third resident block per SM.
+template <bool PROB, int JJ>
+__global__ void __launch_bounds__(32 * WHT_WARPS, JJ <= 12 ? 3 : 2) k_expval_z_wht(const double2* __restrict__ amp,
                                                                  uint64_t nchunks, uint64_t chunk_base,
                                                                  const uint64_t* __restrict__ zmasks,
                                                                  int nterms, double* __restrict__ partials,
                                                                  int partial_stride) {
     __shared__ double wsm[WHT_WARPS][256];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint64_t zt[WHT_JJ];
-    double acc[WHT_JJ];
+    // per term: byte offset of its coefficient in the chunk's table (low 8 mask bits) and the mask
+    // bits above them (at most 32: states have at most 40 qubits, checked by the host)
+    uint32_t zlo[JJ], zhi[JJ];
+    double acc[JJ];
 #pragma unroll
-    for (int jj = 0; jj < WHT_JJ; ++jj) {
+    for (int jj = 0; jj < JJ; ++jj) {
         const int t = jj * 32 + lane;
-        zt[jj] = t < nterms ? zmasks[t] : 0ull;
+        const uint64_t z = t < nterms ? zmasks[t] : 0ull;
+        zlo[jj] = (uint32_t)(z & 255ull) << 3;
+        zhi[jj] = (uint32_t)(z >> 8);
         acc[jj] = 0.0;
     }
     for (uint64_t chunk = blockIdx.x * (uint64_t)WHT_WARPS + warp; chunk < nchunks;
@@ -156,19 +162,20 @@ __global__ void __launch_bounds__(32 * WHT_WARPS) k_expval_z_wht(const double2* 
 #pragma unroll
             for (int r = 0; r < 8; ++r) {
                 const double other = __shfl_xor_sync(0xffffffffu, p[r], o);
-                p[r] = (lane & o) ? other - p[r] : p[r] + other;
+                p[r] = fma((lane & o) ? -1.0 : 1.0, p[r], other);  // other - p / other + p, exactly
             }
         }
 #pragma unroll
         for (int r = 0; r < 8; ++r) wsm[warp][r * 32 + lane] = p[r];
         __syncwarp();
-        const uint64_t gchunk = chunk | chunk_base;
+        const uint32_t gchunk = (uint32_t)(chunk | chunk_base);
+        const char* coef = reinterpret_cast<const char*>(wsm[warp]);
 #pragma unroll
-        for (int jj = 0; jj < WHT_JJ; ++jj) {
+        for (int jj = 0; jj < JJ; ++jj) {
             if (jj * 32 < nterms) {
-                double v = wsm[warp][zt[jj] & 255ull];
-                if (__popcll((zt[jj] >> 8) & gchunk) & 1) v = -v;
-                acc[jj] += v;
+                const double v = *reinterpret_cast<const double*>(coef + zlo[jj]);
+                const int flip = (__popc(zhi[jj] & gchunk) & 1) << 31;  // sign bit of the coefficient
+                acc[jj] += __hiloint2double(__double2hiint(v) ^ flip, __double2loint(v));
             }
         }
         __syncwarp();
@@ -176,7 +183,7 @@ __global__ void __launch_bounds__(32 * WHT_WARPS) k_expval_z_wht(const double2* 
     // reduce the WHT_WARPS warps of the block, term by term
     __syncthreads();
 #pragma unroll
-    for (int jj = 0; jj < WHT_JJ; ++jj) {
+    for (int jj = 0; jj < JJ; ++jj) {
         if (jj * 32 < nterms) {
             wsm[warp][lane] = acc[jj];
             __syncthreads();
@@ -266,11 +273,14 @@ struct TermItem {
 // Z-type terms of `st` (masks in zlist) -> d_res[slot0 ...]; one WHT pass per WHT_TERMS terms.
 static int run_wht_terms(qsv_state* st, const std::vector<uint64_t>& zlist, double* d_res,
                          qsv_counters* ctr, bool prob_layout = false) {
+    if (st->n > 40) QSV_FAIL(QSV_ERR_UNSUPPORTED, "expectation values: more than 40 qubits");
     const uint64_t count = qsv_local_size(st);
     const uint64_t nchunks = count >> 8;
     const uint64_t chunk_base = st->world > 1 ? ((uint64_t)st->rank << (st->n_local - 8)) : 0;
     uint64_t blocks64 = (nchunks + WHT_WARPS - 1) / WHT_WARPS;
-    uint64_t cap = (uint64_t)st->num_sms * 4;
+    // grid-stride kernel: whole waves only (3 resident blocks per SM up to 384 terms, else 2)
+    const size_t most = std::min<size_t>(WHT_TERMS, zlist.size());
+    uint64_t cap = (uint64_t)st->num_sms * (most <= 384 ? 3 : 4);
     if (blocks64 > cap) blocks64 = cap;
     const int blocks = (int)blocks64;
     // scratch (of st): [partials WHT_TERMS x blocks][z masks WHT_TERMS]
@@ -284,12 +294,21 @@ static int run_wht_terms(qsv_state* st, const std::vector<uint64_t>& zlist, doub
         // pageable source: the copy is staged by the runtime before the call returns
         QSV_CUDA(cudaMemcpyAsync(d_z, zlist.data() + p0, nt * sizeof(uint64_t), cudaMemcpyHostToDevice,
                                  st->stream));
-        if (prob_layout)
-            k_expval_z_wht<true><<<blocks, 32 * WHT_WARPS, 0, st->stream>>>(st->amp, nchunks, chunk_base, d_z, nt,
-                                                                            d_part, blocks);
-        else
-            k_expval_z_wht<false><<<blocks, 32 * WHT_WARPS, 0, st->stream>>>(st->amp, nchunks, chunk_base, d_z, nt,
-                                                                             d_part, blocks);
+#define QSV_WHT_LAUNCH(PROB, JJ) \
+    k_expval_z_wht<PROB, JJ><<<blocks, 32 * WHT_WARPS, 0, st->stream>>>(st->amp, nchunks, chunk_base, d_z, nt, d_part, blocks)
+        const int jj = (nt + 31) / 32;
+        if (prob_layout) {
+            if (jj <= 4) QSV_WHT_LAUNCH(true, 4);
+            else if (jj <= 8) QSV_WHT_LAUNCH(true, 8);
+            else if (jj <= 12) QSV_WHT_LAUNCH(true, 12);
+            else QSV_WHT_LAUNCH(true, 16);
+        } else {
+            if (jj <= 4) QSV_WHT_LAUNCH(false, 4);
+            else if (jj <= 8) QSV_WHT_LAUNCH(false, 8);
+            else if (jj <= 12) QSV_WHT_LAUNCH(false, 12);
+            else QSV_WHT_LAUNCH(false, 16);
+        }
+#undef QSV_WHT_LAUNCH
         k_reduce_partials<<<nt, EV_THREADS, 0, st->stream>>>(d_part, blocks, blocks, d_res + p0);
         QSV_CUDA(cudaGetLastError());
         ctr->kernel_launches += 2;
