@@ -545,7 +545,8 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
                 hg.k = 1;
                 memset(hg.q, 0, sizeof hg.q);
                 hg.q[0] = q;
-                if (have == 0 && want == 2) {  // S^dagger as a diagonal gate (joins the pass's phase table), then H
+                static const bool fold_sdg = getenv("QSV_NO_D1RY") == nullptr;
+                if (have == 0 && want == 2 && !fold_sdg) {  // S^dagger as a diagonal gate (a phase table), then H
                     hg.diag = true;
                     hg.m = {cplx(1.0, 0.0), -I};
                     layer.push_back(hg);
@@ -553,7 +554,10 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
                 hg.diag = false;
                 hg.m.resize(4);
                 if (have == 0) {
-                    for (int i = 0; i < 4; ++i) hg.m[i] = vx[i];
+                    // Y: H S^dagger as ONE gate -- real H applied to (a0, -i a1), and -i is a swap of
+                    // components (FP_D1RY): no phase table, the FP64 work of the X family
+                    const cplx* v0 = (want == 2 && fold_sdg) ? vy : vx;
+                    for (int i = 0; i < 4; ++i) hg.m[i] = v0[i];
                 } else {
                     const cplx* vn = want == 1 ? vx : (want == 2 ? vy : id);
                     const cplx* vc = have == 1 ? vx : vy;

@@ -31,7 +31,7 @@
 #define FP_MAX_DIAGS 40  // diagonal ops per pass
 #define FP_NOCOEF 0xffffffffu
 
-enum { FP_D1C = 0, FP_D1R = 1, FP_D2C = 2, FP_D2R = 3, FP_DIAG = 4, FP_DIAGU = 5, FP_D1L = 6 };
+enum { FP_D1C = 0, FP_D1R = 1, FP_D2C = 2, FP_D2R = 3, FP_DIAG = 4, FP_DIAGU = 5, FP_D1L = 6, FP_D1RY = 7 };
 
 struct FpPhase {           // 80 bytes
     uint16_t rd[16];       // register r is read from byte offset (thread offset ^ rd[r]) of the tile buffer
@@ -138,6 +138,20 @@ __device__ __forceinline__ void fp_d1r(double2 (&v)[16], const FpPass& P, int mo
     for (int i = 0; i < 16; ++i) {
         if (i & (1 << B)) continue;
         const double2 a0 = v[i], a1 = v[i | (1 << B)];
+        v[i] = make_double2(fma(m01, a1.x, m00 * a0.x), fma(m01, a1.y, m00 * a0.y));
+        v[i | (1 << B)] = make_double2(fma(m11, a1.x, m10 * a0.x), fma(m11, a1.y, m10 * a0.y));
+    }
+}
+
+// R * diag(1, -i) with R real (H S^dagger, the change to the Y basis): -i only swaps and negates the
+// components of the second amplitude, so the gate costs what the real R costs
+template <int B>
+__device__ __forceinline__ void fp_d1ry(double2 (&v)[16], const FpPass& P, int mo) {
+    const double m00 = P.mats[mo + 0], m01 = P.mats[mo + 1], m10 = P.mats[mo + 2], m11 = P.mats[mo + 3];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        if (i & (1 << B)) continue;
+        const double2 a0 = v[i], a1 = make_double2(v[i | (1 << B)].y, -v[i | (1 << B)].x);
         v[i] = make_double2(fma(m01, a1.x, m00 * a0.x), fma(m01, a1.y, m00 * a0.y));
         v[i | (1 << B)] = make_double2(fma(m11, a1.x, m10 * a0.x), fma(m11, a1.y, m10 * a0.y));
     }
@@ -252,6 +266,10 @@ __device__ __forceinline__ void fp_apply(double2 (&v)[16], const FpPass& P, int 
         case FP_D1R * 16 + 1: fp_d1r<1>(v, P, mo); break;
         case FP_D1R * 16 + 2: fp_d1r<2>(v, P, mo); break;
         case FP_D1R * 16 + 3: fp_d1r<3>(v, P, mo); break;
+        case FP_D1RY * 16 + 0: fp_d1ry<0>(v, P, mo); break;
+        case FP_D1RY * 16 + 1: fp_d1ry<1>(v, P, mo); break;
+        case FP_D1RY * 16 + 2: fp_d1ry<2>(v, P, mo); break;
+        case FP_D1RY * 16 + 3: fp_d1ry<3>(v, P, mo); break;
         case FP_D1L * 16 + 0: fp_d1l<0>(v, P, mo); break;
         case FP_D1L * 16 + 1: fp_d1l<1>(v, P, mo); break;
         case FP_D1L * 16 + 2: fp_d1l<2>(v, P, mo); break;

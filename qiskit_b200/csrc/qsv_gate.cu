@@ -839,6 +839,11 @@ static void fuse_gates(std::vector<HGate>& gates, int nbits) {
 // phase tables of the pass (shared by all register bits of a phase, merged with neighbouring RZ /
 // RZZ / CP gates).  RX = S^dagger RY S is the typical case (Trotter circuits).  Only exact
 // reconstructions are taken (unitary input, both |U00| and |U10| well away from 0).
+// R * diag(1, -i) with R real: first column real, second column purely imaginary (FP_D1RY)
+static bool mat_is_real_times_sdg(const std::vector<cplx>& m) {
+    return m.size() == 4 && m[0].imag() == 0.0 && m[2].imag() == 0.0 && m[1].real() == 0.0 && m[3].real() == 0.0;
+}
+
 static void split_complex_1q(std::vector<HGate>& gates) {
     static const bool enabled = !getenv("QSV_NO_ZYZ");
     if (!enabled || gates.size() < 2) return;
@@ -846,7 +851,7 @@ static void split_complex_1q(std::vector<HGate>& gates) {
     out.reserve(gates.size() + 8);
     for (HGate& g : gates) {
         bool done = false;
-        if (g.k == 1 && !g.diag && g.m.size() == 4 && !mat_is_real(g.m)) {
+        if (g.k == 1 && !g.diag && g.m.size() == 4 && !mat_is_real(g.m) && !mat_is_real_times_sdg(g.m)) {
             const cplx u00 = g.m[0], u01 = g.m[1], u10 = g.m[2], u11 = g.m[3];
             const double c = std::abs(u00), sn = std::abs(u10), c2 = std::abs(u11);
             if (c > 1e-3 && sn > 1e-3 && c2 > 1e-3) {
@@ -2031,6 +2036,16 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
                 sb.kind = op.k == 1 ? (real ? FP_D1R : FP_D1C) : (real ? FP_D2R : FP_D2C);
                 sb.b = op.k == 1 ? (uint8_t)rb[0] : (uint8_t)(rb[order[0]] | (rb[order[1]] << 2));
                 sb.mat = (uint16_t)nmat;
+                if (op.k == 1 && !real && mat_is_real_times_sdg(op.m)) {
+                    sb.kind = FP_D1RY;  // (a0, a1) -> R (a0, -i a1): the cost of the real gate
+                    P.mats[nmat++] = op.m[0].real();
+                    P.mats[nmat++] = -op.m[1].imag();
+                    P.mats[nmat++] = op.m[2].real();
+                    P.mats[nmat++] = -op.m[3].imag();
+                    ++nsubs;
+                    ++cnt;
+                    continue;
+                }
                 if (op.k == 1 && real && use_lifting) {
                     // a plane rotation (c -s ; s c) with c >= 0 (every RY, the real part of a split
                     // RX / U3) runs as three shears: 3 instead of 4 FP64 operations per amplitude
@@ -2109,7 +2124,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
 }
 
 static void trace_fused_pass(const FpPass& P, FILE* f) {
-    int cnt[7] = {0, 0, 0, 0, 0, 0, 0};
+    int cnt[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     fprintf(f, "[fused] T bits:");
     for (int b = 0; b < FP_T; ++b) fprintf(f, " %d", P.pos[b]);
     fprintf(f, " | %sphases %d:", P.warp_local ? "warp-local " : "", P.nphases);
@@ -2118,8 +2133,8 @@ static void trace_fused_pass(const FpPass& P, FILE* f) {
                 P.phases[p].rcoef != FP_NOCOEF ? "r" : "", P.phases[p].wcoef != FP_NOCOEF ? "w" : "");
         for (int i = 0; i < P.phases[p].nsub; ++i) cnt[P.subs[P.phases[p].sub_first + i].kind]++;
     }
-    fprintf(f, " | d1c %d d1r %d d1l %d d2c %d d2r %d diag %d diagu %d | tabs %d\n", cnt[0], cnt[1], cnt[6], cnt[2], cnt[3], cnt[4], cnt[5],
-            P.ntabs);
+    fprintf(f, " | d1c %d d1r %d d1l %d d1ry %d d2c %d d2r %d diag %d diagu %d | tabs %d\n", cnt[0], cnt[1], cnt[6],
+            cnt[7], cnt[2], cnt[3], cnt[4], cnt[5], P.ntabs);
 }
 
 static int upload_product_tables(qsv_state* s, uint64_t neutral, const std::vector<cplx>& extra);
