@@ -531,6 +531,11 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
                 cur_x = cur_z = 0;
             }
             // per rotated qubit: V_new * V_cur^dagger with V_X = H, V_Y = H S^dagger, V_Z = I
+            // From the Z frame, when only |a|^2 of the result is read, the butterflies run without
+            // their 1/sqrt(2): the factor 2^-k of k of them is exact and goes into the term values.
+            static const bool allow_unnorm = getenv("QSV_NO_UNNORM") == nullptr;
+            const bool unnorm = allow_unnorm && last_use && cur_x == 0 && s->n_local <= 60;
+            int n_butterflies = 0;
             std::vector<HGate> layer;
             for (int q = 0; q < s->n_local; ++q) {
                 const uint64_t b = 1ull << q;
@@ -557,7 +562,12 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
                     // Y: H S^dagger as ONE gate -- real H applied to (a0, -i a1), and -i is a swap of
                     // components (FP_D1RY): no phase table, the FP64 work of the X family
                     const cplx* v0 = (want == 2 && fold_sdg) ? vy : vx;
-                    for (int i = 0; i < 4; ++i) hg.m[i] = v0[i];
+                    for (int i = 0; i < 4; ++i) hg.m[i] = unnorm ? v0[i] / r2 : v0[i];
+                    if (unnorm) {  // exactly (1 1 ; 1 -1) or (1 -i ; 1 i), whatever the division rounded to
+                        for (int i = 0; i < 4; ++i)
+                            hg.m[i] = cplx(std::round(hg.m[i].real()), std::round(hg.m[i].imag()));
+                        ++n_butterflies;
+                    }
                 } else {
                     const cplx* vn = want == 1 ? vx : (want == 2 ? vy : id);
                     const cplx* vc = have == 1 ? vx : vy;
@@ -591,7 +601,7 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
                 result_slot[it.idx] = slot + i;
                 // Re((-i)^(sel - ny)) corrects a caller-supplied phase that differs from (-i)^ny
                 const int d = ((it.sel - it.ny) % 4 + 4) % 4;
-                factor[it.idx] = d == 0 ? 1.0 : (d == 2 ? -1.0 : 0.0);
+                factor[it.idx] = (d == 0 ? 1.0 : (d == 2 ? -1.0 : 0.0)) * std::ldexp(1.0, -n_butterflies);
             }
             const bool probs = !layer.empty() && aux->prob_layout;
             QSV_TRY(run_wht_terms(aux, zl, d_res + slot, &s->ctr, probs));

@@ -31,7 +31,7 @@
 #define FP_MAX_DIAGS 40  // diagonal ops per pass
 #define FP_NOCOEF 0xffffffffu
 
-enum { FP_D1C = 0, FP_D1R = 1, FP_D2C = 2, FP_D2R = 3, FP_DIAG = 4, FP_DIAGU = 5, FP_D1L = 6, FP_D1RY = 7 };
+enum { FP_D1C = 0, FP_D1R = 1, FP_D2C = 2, FP_D2R = 3, FP_DIAG = 4, FP_DIAGU = 5, FP_D1L = 6, FP_D1RY = 7, FP_D1H = 8, FP_D1HY = 9 };
 
 struct FpPhase {           // 80 bytes
     uint16_t rd[16];       // register r is read from byte offset (thread offset ^ rd[r]) of the tile buffer
@@ -157,6 +157,21 @@ __device__ __forceinline__ void fp_d1ry(double2 (&v)[16], const FpPass& P, int m
     }
 }
 
+// unnormalised Hadamard butterfly (1 1 ; 1 -1): additions only.  Basis-change expectation values
+// use it when only |a|^2 of the result is read: the factor 2^-k of k butterflies is exact and is
+// applied to the term values on the host.  Y = true: on (a0, -i a1), the Y-basis change.
+template <int B, bool Y>
+__device__ __forceinline__ void fp_d1h(double2 (&v)[16]) {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        if (i & (1 << B)) continue;
+        const double2 a0 = v[i];
+        const double2 a1 = Y ? make_double2(v[i | (1 << B)].y, -v[i | (1 << B)].x) : v[i | (1 << B)];
+        v[i] = make_double2(a0.x + a1.x, a0.y + a1.y);
+        v[i | (1 << B)] = make_double2(a0.x - a1.x, a0.y - a1.y);
+    }
+}
+
 // plane rotation (c -s ; s c), c >= 0, as three shears (lifting): x += t y; y += s x; x += t y with
 // t = -s / (1 + c) -- 3 FMA per real pair instead of 4 operations; |t| <= 1, so no amplification
 template <int B>
@@ -270,6 +285,14 @@ __device__ __forceinline__ void fp_apply(double2 (&v)[16], const FpPass& P, int 
         case FP_D1RY * 16 + 1: fp_d1ry<1>(v, P, mo); break;
         case FP_D1RY * 16 + 2: fp_d1ry<2>(v, P, mo); break;
         case FP_D1RY * 16 + 3: fp_d1ry<3>(v, P, mo); break;
+        case FP_D1H * 16 + 0: fp_d1h<0, false>(v); break;
+        case FP_D1H * 16 + 1: fp_d1h<1, false>(v); break;
+        case FP_D1H * 16 + 2: fp_d1h<2, false>(v); break;
+        case FP_D1H * 16 + 3: fp_d1h<3, false>(v); break;
+        case FP_D1HY * 16 + 0: fp_d1h<0, true>(v); break;
+        case FP_D1HY * 16 + 1: fp_d1h<1, true>(v); break;
+        case FP_D1HY * 16 + 2: fp_d1h<2, true>(v); break;
+        case FP_D1HY * 16 + 3: fp_d1h<3, true>(v); break;
         case FP_D1L * 16 + 0: fp_d1l<0>(v, P, mo); break;
         case FP_D1L * 16 + 1: fp_d1l<1>(v, P, mo); break;
         case FP_D1L * 16 + 2: fp_d1l<2>(v, P, mo); break;

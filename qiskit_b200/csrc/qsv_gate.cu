@@ -2036,6 +2036,14 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
                 sb.kind = op.k == 1 ? (real ? FP_D1R : FP_D1C) : (real ? FP_D2R : FP_D2C);
                 sb.b = op.k == 1 ? (uint8_t)rb[0] : (uint8_t)(rb[order[0]] | (rb[order[1]] << 2));
                 sb.mat = (uint16_t)nmat;
+                if (op.k == 1 && op.m[0] == cplx(1.0, 0.0) && op.m[2] == cplx(1.0, 0.0) &&
+                    ((op.m[1] == cplx(1.0, 0.0) && op.m[3] == cplx(-1.0, 0.0)) ||
+                     (op.m[1] == cplx(0.0, -1.0) && op.m[3] == cplx(0.0, 1.0)))) {
+                    sb.kind = op.m[1].imag() == 0.0 ? FP_D1H : FP_D1HY;  // unnormalised butterfly: additions only
+                    ++nsubs;
+                    ++cnt;
+                    continue;
+                }
                 if (op.k == 1 && !real && mat_is_real_times_sdg(op.m)) {
                     sb.kind = FP_D1RY;  // (a0, a1) -> R (a0, -i a1): the cost of the real gate
                     P.mats[nmat++] = op.m[0].real();
@@ -2124,7 +2132,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
 }
 
 static void trace_fused_pass(const FpPass& P, FILE* f) {
-    int cnt[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int cnt[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     fprintf(f, "[fused] T bits:");
     for (int b = 0; b < FP_T; ++b) fprintf(f, " %d", P.pos[b]);
     fprintf(f, " | %sphases %d:", P.warp_local ? "warp-local " : "", P.nphases);
@@ -2133,8 +2141,8 @@ static void trace_fused_pass(const FpPass& P, FILE* f) {
                 P.phases[p].rcoef != FP_NOCOEF ? "r" : "", P.phases[p].wcoef != FP_NOCOEF ? "w" : "");
         for (int i = 0; i < P.phases[p].nsub; ++i) cnt[P.subs[P.phases[p].sub_first + i].kind]++;
     }
-    fprintf(f, " | d1c %d d1r %d d1l %d d1ry %d d2c %d d2r %d diag %d diagu %d | tabs %d\n", cnt[0], cnt[1], cnt[6],
-            cnt[7], cnt[2], cnt[3], cnt[4], cnt[5], P.ntabs);
+    fprintf(f, " | d1c %d d1r %d d1l %d d1ry %d d1h %d d2c %d d2r %d diag %d diagu %d | tabs %d\n", cnt[0], cnt[1], cnt[6],
+            cnt[7], cnt[8] + cnt[9], cnt[2], cnt[3], cnt[4], cnt[5], P.ntabs);
 }
 
 static int upload_product_tables(qsv_state* s, uint64_t neutral, const std::vector<cplx>& extra);
