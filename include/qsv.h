@@ -75,6 +75,8 @@ typedef struct qsv_counters {
     uint64_t swap_count;      /* sharded states: global<->local qubit exchanges */
     uint64_t swap_bytes;      /* bytes this rank sent over NVLink in those exchanges */
     uint64_t write_passes;    /* write-only sweeps (basis / product-state initialisation) */
+    uint64_t swap_ns;         /* device time spent in those exchanges (CUDA events, nanoseconds) */
+    uint64_t fused_swaps;     /* exchanges that rode inside the following fused gate pass (no standalone kernel) */
 } qsv_counters;
 
 /* ---- library ---------------------------------------------------------- */
@@ -139,6 +141,10 @@ int qsv_sample(const qsv_state* s, const int* qargs, int m, const double* unifor
  * rotate_to_zero the kept branch is moved to the qargs = 0...0 branch. */
 int qsv_collapse(qsv_state* s, const int* qargs, int m, uint64_t outcome, double scale,
                  int rotate_to_zero);
+/* probabilities(qargs)[outcome], clipped to [0, 1]: the single entry of the marginal that
+ * Statevector.reset (statevector.py:705-712) and QuantumState.measure (quantum_state.py:317-324)
+ * normalise by -- one read pass, 8 bytes back instead of the whole 2^m array */
+int qsv_outcome_probability(const qsv_state* s, const int* qargs, int m, uint64_t outcome, double* out);
 /* StatevectorSampler._samples_to_packed_array (statevector_sampler.py:235-251):
  * indices[shots] -> out[shots * num_bytes]; clbit c takes bit src_bit[c] of the
  * index (src_bit[c] < 0: constant 0); big-endian bytes, clbit 0 = LSB of the last
@@ -213,6 +219,12 @@ int qsv_sample_counts(int device, const uint64_t* keys, uint64_t n, uint64_t* ou
 /* ---- measurement hooks -------------------------------------------------- */
 int qsv_get_counters(const qsv_state* s, qsv_counters* out);
 int qsv_reset_counters(qsv_state* s);
+/* the same counters summed over every handle this process has had (live, destroyed or reset):
+ * what bench.py reports for a public-API call that creates its handles internally */
+int qsv_process_counters(qsv_counters* out);
+/* put every tunable of qsv_set_option back to the library default (a pooled handle must not carry
+ * one user's experiment switches over to the next) */
+int qsv_restore_defaults(qsv_state* s);
 /* CUDA-event timer on the handle's stream: begin records an event, end records a
  * second one, synchronises and returns the elapsed milliseconds between them. */
 int qsv_timer_begin(qsv_state* s);

@@ -46,6 +46,8 @@ class QsvCounters(C.Structure):
         ("swap_count", C.c_uint64),
         ("swap_bytes", C.c_uint64),
         ("write_passes", C.c_uint64),
+        ("swap_ns", C.c_uint64),
+        ("fused_swaps", C.c_uint64),
     ]
 
 
@@ -77,6 +79,7 @@ PROTOTYPES = {
     "qsv_probabilities": (_i, [_vp, _P(_i), _i, _vp]),
     "qsv_sample": (_i, [_vp, _P(_i), _i, _vp, _u64, _vp, _P(_dbl)]),
     "qsv_collapse": (_i, [_vp, _P(_i), _i, _u64, _dbl, _i]),
+    "qsv_outcome_probability": (_i, [_vp, _P(_i), _i, _u64, _P(_dbl)]),
     "qsv_pack_samples": (_i, [_vp, _u64, _P(_i), _i, _vp]),
     "qsv_permute_qubits": (_i, [_vp, _vp, _P(_i)]),
     "qsv_tensor": (_i, [_vp, _vp, _vp, _P(_i), _P(_i), _i]),
@@ -92,6 +95,8 @@ PROTOTYPES = {
     "qsv_sample_counts": (_i, [_i, _vp, _u64, _vp, _vp, _P(_u64)]),
     "qsv_get_counters": (_i, [_vp, _P(QsvCounters)]),
     "qsv_reset_counters": (_i, [_vp]),
+    "qsv_process_counters": (_i, [_P(QsvCounters)]),
+    "qsv_restore_defaults": (_i, [_vp]),
     "qsv_timer_begin": (_i, [_vp]),
     "qsv_timer_end": (_i, [_vp, _P(C.c_float)]),
     "qsv_set_option": (_i, [_vp, C.c_char_p, C.c_int64]),
@@ -198,10 +203,17 @@ def release(handle, n_qubits: int, device: int = 0):
         return
     with _pool_lock:
         free = _pool.setdefault((n_qubits, device), [])
-        if len(free) < _POOL_MAX_PER_KEY:
-            free.append(handle)
+        if len(free) < _POOL_MAX_PER_KEY and _lib.qsv_restore_defaults(handle) == QSV_OK:
+            free.append(handle)   # tunables back to the defaults: the next owner starts clean
             return
     _lib.qsv_destroy(handle)
+
+
+def process_counters() -> dict:
+    """Counters summed over every handle of this process (qsv_process_counters)."""
+    c = QsvCounters()
+    check(load().qsv_process_counters(C.byref(c)))
+    return {name: int(getattr(c, name)) for name, _ in c._fields_}
 
 
 def drain_pool():

@@ -87,12 +87,29 @@ struct qsv_dist {
     void* xbuf;                    // NCCL transport scratch
     size_t xbuf_bytes;
     int min_lpos;                  // lowest local bit position the planner may evict
+    // device time of the exchanges: event pairs recorded around every swap, folded into
+    // ctr.swap_ns when somebody reads the counters (no synchronisation on the hot path)
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timers;
 };
+
+void qsv_dist_collect_times(qsv_state* s) {
+    qsv_dist* d = s->dist;
+    if (!d) return;
+    for (auto& pr : d->timers) {
+        float ms = 0.f;
+        if (cudaEventSynchronize(pr.second) == cudaSuccess && cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess)
+            s->ctr.swap_ns += (uint64_t)((double)ms * 1e6);
+        cudaEventDestroy(pr.first);
+        cudaEventDestroy(pr.second);
+    }
+    d->timers.clear();
+}
 
 void qsv_dist_free(qsv_state* s) {
     qsv_dist* d = s->dist;
     if (!d) return;
     cudaStreamSynchronize(s->stream);
+    qsv_dist_collect_times(s);
     for (int r = 0; r < s->world; ++r)
         if (d->ipc_base[r]) cudaIpcCloseMemHandle(d->ipc_base[r]);
     if (d->d_tok) cudaFree(d->d_tok);
@@ -155,8 +172,7 @@ extern "C" int qsv_create_dist(qsv_state** out, int n_qubits, int device, int ra
     QSV_TRY(qsv_state_alloc(&s, n_qubits, n_qubits - g, device, nullptr));
     s->rank = rank;
     s->world = world;
-    qsv_dist* d = new qsv_dist();
-    memset(d, 0, sizeof *d);
+    qsv_dist* d = new qsv_dist();  // value-initialised: every field zero, the timer list empty
     d->g = g;
     s->dist = d;
     d->min_lpos = s->n_local >= 16 ? 5 : 0;
@@ -371,11 +387,9 @@ static int dist_swap_bits(qsv_state* s, int k, const int* gpos, const int* lpos)
     const int npeers = (1 << k) - 1;
     static const bool trace = getenv("QSV_TRACE") != nullptr;
     cudaEvent_t te0 = nullptr, te1 = nullptr;
-    if (trace) {
-        QSV_CUDA(cudaEventCreate(&te0));
-        QSV_CUDA(cudaEventCreate(&te1));
-        QSV_CUDA(cudaEventRecord(te0, s->stream));
-    }
+    QSV_CUDA(cudaEventCreate(&te0));
+    QSV_CUDA(cudaEventCreate(&te1));
+    QSV_CUDA(cudaEventRecord(te0, s->stream));
     if (d->use_p2p) {
         QSV_TRY(dist_barrier(s));
         uint64_t blocks = ((A.rest >> 1) + 256 * 4 - 1) / (256 * 4);
@@ -421,13 +435,12 @@ static int dist_swap_bits(qsv_state* s, int k, const int* gpos, const int* lpos)
             s->ctr.kernel_launches += 2;
         }
     }
+    QSV_CUDA(cudaEventRecord(te1, s->stream));
+    d->timers.emplace_back(te0, te1);
     if (trace) {
         float ms = 0.f;
-        QSV_CUDA(cudaEventRecord(te1, s->stream));
         QSV_CUDA(cudaEventSynchronize(te1));
         QSV_CUDA(cudaEventElapsedTime(&ms, te0, te1));
-        cudaEventDestroy(te0);
-        cudaEventDestroy(te1);
         const double gb = (double)npeers * A.rest * 16 / 1e9;
         if (s->rank == 0)
             fprintf(stderr, "[swap] k=%d %s sent %.2f GB/rank in %.3f ms = %.1f GB/s per direction\n", k,

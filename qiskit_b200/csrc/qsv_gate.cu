@@ -2058,7 +2058,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
                     // a plane rotation (c -s ; s c) with c >= 0 (every RY, the real part of a split
                     // RX / U3) runs as three shears: 3 instead of 4 FP64 operations per amplitude
                     const double c = op.m[0].real(), ms = op.m[1].real(), sn = op.m[2].real(), c1 = op.m[3].real();
-                    if (c == c1 && ms == -sn && c >= 0.0 && std::abs(c * c + sn * sn - 1.0) < 1e-14) {
+                    if (c == c1 && ms == -sn && c >= 0.0 && std::abs(c * c + sn * sn - 1.0) <= 4.5e-16) {  // the bound of split_complex_1q: the shears reproduce the matrix to ~1 ulp
                         sb.kind = FP_D1L;
                         P.mats[nmat++] = -sn / (1.0 + c);
                         P.mats[nmat++] = sn;

@@ -276,33 +276,65 @@ __global__ void k_clip01(double* p, uint64_t n) {
     for (; i < n; i += stride) p[i] = fmin(fmax(p[i], 0.0), 1.0);
 }
 
-// keep the branch where the gathered bits equal `outcome`, scaled; zero the rest
-__global__ void k_collapse(double2* __restrict__ amp, uint64_t groups, GatherBits G, uint64_t outcome,
-                           double scale, int rotate) {
-    int sorted[64];
-    for (int j = 0; j < G.m; ++j) sorted[j] = G.bit[j];
-    for (int a = 1; a < G.m; ++a) {
-        int v = sorted[a], b = a - 1;
-        while (b >= 0 && sorted[b] > v) { sorted[b + 1] = sorted[b]; --b; }
-        sorted[b + 1] = v;
-    }
-    uint64_t keep_off = 0;
-    for (int j = 0; j < G.m; ++j) keep_off |= ((outcome >> j) & 1ull) << G.bit[j];
-    const uint64_t dst_off = rotate ? 0 : keep_off;
-    const uint64_t members = 1ull << G.m;
-    uint64_t g = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+// keep the branch where the masked index bits equal `keep`, scaled; zero the rest.  One thread per
+// amplitude, any number of measured bits.  rotate: the kept branch moves to the masked bits = 0
+// branch; the pair (i, i | keep) is then owned by the thread whose masked bits are zero.
+__global__ void __launch_bounds__(256) k_collapse(double2* __restrict__ amp, uint64_t count, uint64_t mask,
+                                                  uint64_t keep, double scale, int rotate) {
+    uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    for (; g < groups; g += stride) {
-        uint64_t base = g;
-        for (int j = 0; j < G.m; ++j) base = insert_zero(base, sorted[j]);
-        double2 v = amp[base | keep_off];
-        v.x *= scale;
-        v.y *= scale;
-        for (uint64_t c = 0; c < members; ++c) {
-            uint64_t off = 0;
-            for (int j = 0; j < G.m; ++j) off |= ((c >> j) & 1ull) << G.bit[j];
-            amp[base | off] = off == dst_off ? v : make_double2(0.0, 0.0);
+    const double2 zero = make_double2(0.0, 0.0);
+    for (; i < count; i += stride) {
+        const uint64_t c = i & mask;
+        if (!rotate || keep == 0) {
+            if (c == keep) {
+                double2 v = amp[i];
+                amp[i] = make_double2(v.x * scale, v.y * scale);
+            } else {
+                amp[i] = zero;
+            }
+        } else if (c == 0) {
+            double2 v = amp[i | keep];
+            amp[i] = make_double2(v.x * scale, v.y * scale);
+            amp[i | keep] = zero;
+        } else if (c != keep) {
+            amp[i] = zero;
         }
+    }
+}
+
+// partial sums of |a_i|^2 over the amplitudes whose masked index bits equal `keep`
+__global__ void __launch_bounds__(256) k_masked_norm(const double2* __restrict__ amp, uint64_t count, uint64_t mask,
+                                                     uint64_t keep, double* __restrict__ partials) {
+    __shared__ double sh[8];
+    double acc = 0.0;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < count; i += stride) {
+        if ((i & mask) != keep) continue;
+        const double2 a = amp[i];
+        acc += a.x * a.x + a.y * a.y;
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        double v = threadIdx.x < 8 ? sh[threadIdx.x] : 0.0;
+        v = warp_sum(v);
+        if (threadIdx.x == 0) partials[blockIdx.x] = v;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_sum_partials(const double* __restrict__ partials, int n, double* __restrict__ out) {
+    __shared__ double sh[8];
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n; i += 256) acc += partials[i];
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        double v = threadIdx.x < 8 ? sh[threadIdx.x] : 0.0;
+        v = warp_sum(v);
+        if (threadIdx.x == 0) out[0] = v;
     }
 }
 
@@ -515,12 +547,50 @@ extern "C" int qsv_collapse(qsv_state* s, const int* qargs, int m, uint64_t outc
     bool identity;
     QSV_TRY(resolve_qargs(s, qargs, m, G, identity, "qsv_collapse"));
     if (m < 64 && outcome >> m) QSV_FAIL(QSV_ERR_INVALID, "qsv_collapse: outcome out of range");
-    if (m > 20) QSV_FAIL(QSV_ERR_UNSUPPORTED, "qsv_collapse: more than 20 measured qubits");
-    const uint64_t groups = 1ull << (s->n_local - m);
-    k_collapse<<<cap_blocks(s, groups, 128), 128, 0, s->stream>>>(s->amp, groups, G, outcome, scale,
-                                                                  rotate_to_zero);
+    uint64_t mask = 0, keep = 0;
+    for (int j = 0; j < m; ++j) {
+        mask |= 1ull << G.bit[j];
+        keep |= ((outcome >> j) & 1ull) << G.bit[j];
+    }
+    const uint64_t count = qsv_local_size(s);
+    k_collapse<<<cap_blocks(s, count, 256), 256, 0, s->stream>>>(s->amp, count, mask, keep, scale, rotate_to_zero);
     QSV_CUDA(cudaGetLastError());
     s->ctr.kernel_launches++;
     s->ctr.state_passes++;
+    return QSV_OK;
+}
+
+// probability of ONE outcome of the marginal on qargs: the value Statevector.reset / measure divide by
+// (statevector.py:705-712, quantum_state.py:317-324 read it out of the full marginal array)
+extern "C" int qsv_outcome_probability(const qsv_state* cs, const int* qargs, int m, uint64_t outcome, double* out) {
+    qsv_state* s = const_cast<qsv_state*>(cs);
+    if (!s || !out || (!qargs && m)) QSV_FAIL(QSV_ERR_INVALID, "qsv_outcome_probability: NULL argument");
+    QSV_CUDA(cudaSetDevice(s->device));
+    QSV_TRY(qsv_materialize(s));
+    if (s->world > 1) QSV_FAIL(QSV_ERR_UNSUPPORTED, "qsv_outcome_probability: sharded states");
+    GatherBits G;
+    bool identity;
+    QSV_TRY(resolve_qargs(s, qargs, m, G, identity, "qsv_outcome_probability"));
+    if (m < 64 && outcome >> m) QSV_FAIL(QSV_ERR_INVALID, "qsv_outcome_probability: outcome out of range");
+    uint64_t mask = 0, keep = 0;
+    for (int j = 0; j < m; ++j) {
+        mask |= 1ull << G.bit[j];
+        keep |= ((outcome >> j) & 1ull) << G.bit[j];
+    }
+    const uint64_t count = qsv_local_size(s);
+    const int blocks = cap_blocks(s, count, 256);
+    QSV_TRY(qsv_ensure_scratch(s, (size_t)(blocks + 1) * sizeof(double) + 256));
+    QSV_TRY(qsv_ensure_pinned(s, 64));
+    double* d_part = (double*)s->scratch;
+    k_masked_norm<<<blocks, 256, 0, s->stream>>>(s->amp, count, mask, keep, d_part + 1);
+    k_sum_partials<<<1, 256, 0, s->stream>>>(d_part + 1, blocks, d_part);
+    QSV_CUDA(cudaGetLastError());
+    s->ctr.kernel_launches += 2;
+    s->ctr.read_passes++;
+    QSV_CUDA(cudaMemcpyAsync(s->pinned, d_part, sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+    QSV_CUDA(cudaStreamSynchronize(s->stream));
+    s->ctr.d2h_bytes += sizeof(double);
+    const double p = *(const double*)s->pinned;
+    *out = p < 0.0 ? 0.0 : (p > 1.0 ? 1.0 : p);  // np.clip of Statevector.probabilities (statevector.py:668)
     return QSV_OK;
 }

@@ -1,7 +1,29 @@
 // State lifetime, transfers, counters, timers.  C ABI: include/qsv.h.
 #include "qsv_common.cuh"
 
+#include <mutex>
+
 static thread_local std::string g_last_error;
+
+// process-wide view of the per-handle counters: live handles + what retired / reset handles had
+static std::mutex g_reg_mutex;
+static std::vector<qsv_state*> g_live;
+static qsv_counters g_retired;
+
+static void ctr_add(qsv_counters& a, const qsv_counters& b) {
+    a.kernel_launches += b.kernel_launches;
+    a.state_passes += b.state_passes;
+    a.read_passes += b.read_passes;
+    a.gates_applied += b.gates_applied;
+    a.h2d_bytes += b.h2d_bytes;
+    a.d2h_bytes += b.d2h_bytes;
+    a.phases += b.phases;
+    a.swap_count += b.swap_count;
+    a.swap_bytes += b.swap_bytes;
+    a.write_passes += b.write_passes;
+    a.swap_ns += b.swap_ns;
+    a.fused_swaps += b.fused_swaps;
+}
 
 void qsv_set_error(const char* fmt, ...) {
     char buf[1024];
@@ -133,6 +155,10 @@ int qsv_state_alloc(qsv_state** out, int n_qubits, int n_local, int device, cuda
     QSV_CUDA(cudaGetDeviceProperties(&prop, device));
     s->num_sms = prop.multiProcessorCount;
     qsv_state_defaults(s);
+    if (!share_stream) {  // scratch copies on a shared stream report through their owner's counters
+        std::lock_guard<std::mutex> lk(g_reg_mutex);
+        g_live.push_back(s);
+    }
     *out = s;
     return QSV_OK;
 }
@@ -143,12 +169,22 @@ extern "C" int qsv_create(qsv_state** out, int n_qubits, int device) {
 }
 
 void qsv_dist_free(qsv_state* s);  // qsv_dist.cu
+void qsv_dist_collect_times(qsv_state* s);
 int qsv_dist_set_option(qsv_state* s, const char* name, int64_t value);
 
 extern "C" int qsv_destroy(qsv_state* s) {
     if (!s) return QSV_OK;
     cudaSetDevice(s->device);
     cudaStreamSynchronize(s->stream);
+    {
+        std::lock_guard<std::mutex> lk(g_reg_mutex);
+        for (size_t i = 0; i < g_live.size(); ++i)
+            if (g_live[i] == s) {
+                g_live.erase(g_live.begin() + i);
+                ctr_add(g_retired, s->ctr);
+                break;
+            }
+    }
     if (s->dist) qsv_dist_free(s);
     if (s->aux) {
         qsv_destroy(s->aux);
@@ -297,13 +333,31 @@ extern "C" int qsv_sync(const qsv_state* s) {
 
 extern "C" int qsv_get_counters(const qsv_state* s, qsv_counters* out) {
     if (!s || !out) QSV_FAIL(QSV_ERR_INVALID, "qsv_get_counters: NULL argument");
+    if (s->dist) qsv_dist_collect_times(const_cast<qsv_state*>(s));  // folds finished swap timers into ctr.swap_ns
     *out = s->ctr;
     return QSV_OK;
 }
 
 extern "C" int qsv_reset_counters(qsv_state* s) {
     if (!s) QSV_FAIL(QSV_ERR_INVALID, "qsv_reset_counters: state is NULL");
+    std::lock_guard<std::mutex> lk(g_reg_mutex);
+    if (s->owns_stream) ctr_add(g_retired, s->ctr);
     memset(&s->ctr, 0, sizeof s->ctr);
+    return QSV_OK;
+}
+
+extern "C" int qsv_process_counters(qsv_counters* out) {
+    if (!out) QSV_FAIL(QSV_ERR_INVALID, "qsv_process_counters: out is NULL");
+    std::lock_guard<std::mutex> lk(g_reg_mutex);
+    *out = g_retired;
+    for (const qsv_state* s : g_live) ctr_add(*out, s->ctr);
+    return QSV_OK;
+}
+
+extern "C" int qsv_restore_defaults(qsv_state* s) {
+    if (!s) QSV_FAIL(QSV_ERR_INVALID, "qsv_restore_defaults: state is NULL");
+    qsv_state_defaults(s);  // a pending lazy |index> stays pending: qsv_materialize does not consult the option
+    if (s->aux) qsv_state_defaults(s->aux), s->aux->lazy_init = 0;
     return QSV_OK;
 }
 

@@ -399,7 +399,10 @@ class DensityMatrix:
             _lib.check(lib.qsv_init_basis(self._h, 0))
             return
         qa = self._qargs(qargs)
-        _lib.check(lib.qsv_density_reset(self._h, _lib.int_array(qa), len(qa)))
+        # the reset channel factors per qubit: chunks of <= 10 qubits (the kernel's group size)
+        for i in range(0, len(qa), 10):
+            part = qa[i:i + 10]
+            _lib.check(lib.qsv_density_reset(self._h, _lib.int_array(part), len(part)))
 
     def reset(self, qargs=None):
         """densitymatrix.py:508-537 (deterministic: the reset channel, no sampling)."""
@@ -510,11 +513,16 @@ class DensityMatrix:
         probs = self.probabilities(qa)
         sample = self._rng.choice(len(probs), p=probs, size=1)
         outcome = str(_ket_strings(sample, len(qa))[0])
-        proj = np.zeros(len(probs), dtype=complex)
-        proj[sample] = 1 / np.sqrt(probs[sample])
+        # the projector |s><s| / sqrt(p) is a product over qubits: diagonals of <= 8 qubits each
+        # (the reference builds the full 2^m diagonal, quantum_state.py:321-329), the scale on the first
+        idx = int(sample[0])
         ret = self._new_like()
         stream = _DensityStream(self._n)
-        stream.diagonal(proj, qa)
+        for i in range(0, len(qa), 8):
+            part = qa[i:i + 8]
+            proj = np.zeros(1 << len(part), dtype=complex)
+            proj[(idx >> i) & ((1 << len(part)) - 1)] = 1 / np.sqrt(probs[idx]) if i == 0 else 1.0
+            stream.diagonal(proj, part)
         ret._flush(stream)
         return outcome, ret
 

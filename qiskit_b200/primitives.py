@@ -418,7 +418,9 @@ class SamplerPub:
 def _has_reset(circuit) -> bool:
     for inst in circuit:
         op = inst.operation
-        if getattr(op, "name", None) == "reset":
+        # `initialize` on a subset of qubits resets them first (statevector.py:989-1014): it draws
+        # from the state's RNG exactly like `reset`, so it is just as stochastic
+        if getattr(op, "name", None) in ("reset", "initialize"):
             return True
         d = getattr(op, "definition", None)
         if d is not None and hasattr(d, "__iter__") and _has_reset(d):

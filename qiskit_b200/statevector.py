@@ -511,8 +511,10 @@ class Statevector:
         """One outcome and its (clipped) probability, consuming one uniform like
         ``rng.choice(len(probs), p=probs, size=1)`` (statevector.py:705)."""
         idx = int(self.sample_indices(1, qargs)[0])
-        prob = float(self.probabilities(qargs)[idx])
-        return idx, prob
+        prob = C.c_double()
+        _lib.check(_lib.load().qsv_outcome_probability(self._h, _lib.int_array(qargs), len(qargs), idx,
+                                                       C.byref(prob)))
+        return idx, prob.value
 
     def measure(self, qargs=None):
         """quantum_state.py:296-331 -> (outcome string, collapsed state)."""

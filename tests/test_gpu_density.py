@@ -7,6 +7,7 @@ import pytest
 
 from helpers import oracle_matrices, random_named_circuit, random_state, random_unitary
 from oracle import density_ref as dref
+from oracle import gate_matrices as ogm
 from oracle import statevector_ref as ref
 from qiskit_b200 import DensityMatrix, Pauli, QiskitError, SparsePauliOp, Statevector
 from qiskit_b200 import circuit_library as lib
@@ -232,3 +233,21 @@ def test_larger_density_matrix_properties():
     np.testing.assert_allclose(dm.probabilities([0, 5, 11]), sv.probabilities([0, 5, 11]), atol=TOL)
     mixed = dm.reset([0, 1])
     assert abs(mixed.trace() - 1) < TOL and mixed.purity().real < 1 - 1e-3
+
+
+def test_density_reset_and_measure_on_all_twelve_qubits():
+    """reset / measure with more qubits than one kernel call or one diagonal takes:
+    the channel and the projector factor per qubit, so the host applies them in chunks."""
+    n = 12
+    rng = np.random.default_rng(4)
+    gates = [(ogm.ry(float(t)), [q]) for q, t in enumerate(rng.uniform(0.3, 2.8, n))] + \
+            [(ogm.cx(), [q, q + 1]) for q in range(0, n - 1, 2)]
+    rho = DensityMatrix.from_int(0, 1 << n)
+    rho.apply_gate_list(gates)
+    got = rho.reset(list(range(n))).data          # every qubit reset -> |0..0><0..0| (trace 1)
+    assert abs(got[0, 0] - 1.0) < 1e-10 and np.count_nonzero(np.abs(got) > 1e-10) == 1
+    rho.seed(9)
+    outcome, post = rho.measure()
+    idx = int(outcome, 2)
+    d = post.data
+    assert abs(d[idx, idx] - 1.0) < 1e-9 and np.count_nonzero(np.abs(d) > 1e-9) == 1

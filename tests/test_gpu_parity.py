@@ -594,6 +594,32 @@ def test_estimator_reset_trajectories_reproducible():
     np.testing.assert_allclose(a, [np.cos(0.3), np.sin(0.3)], atol=1e-12)
 
 
+def test_estimator_initialize_on_entangled_subset_is_stochastic_and_seeded():
+    """`initialize` on a subset resets those qubits first (statevector.py:989-1014): it draws from the
+    state's rng like `reset`, so the Estimator must re-simulate every index from the pub's ONE seeded
+    generator (statevector_estimator.py:151,160-171) -- the reset draw and the precision noise interleave."""
+    s2 = np.sqrt(0.5)
+    qc = QuantumCircuit(2); qc.h(0); qc.cx(0, 1); qc.initialize([s2, s2], [0]); qc.ry(Parameter("a"), 1)
+    obs = ["ZI", "IX", "ZZ"]
+    run = lambda seed: StatevectorEstimator(seed=seed, default_precision=0.1).run(  # noqa: E731
+        [(qc, obs, [[0.4]])]).result()[0].data.evs
+    a, b = run(21), run(21)
+    np.testing.assert_array_equal(a, b)
+    # the oracle's serial loop with the same generator: per index reset draw, then noise
+    rng = np.random.default_rng(21)
+    want = []
+    hmat, cx = ogm.h(), ogm.cx()
+    init = np.zeros((2, 2), complex); init[:, 0] = [s2, s2]
+    for label in obs:
+        psi = ref.evolve_operator(ref.evolve_operator(ref.basis_state(2), hmat, [0]), cx, [0, 1])
+        psi = ref.reset(psi, [0], rng)
+        psi = ref.evolve_operator(psi, init, [0])
+        psi = ref.evolve_operator(psi, ogm.ry(0.4), [1])
+        ev = np.real_if_close(ref.expectation_value_labels(psi, [(label, 1.0)]))
+        want.append(rng.normal(ev, 0.1))
+    np.testing.assert_allclose(a, want, atol=1e-10)
+
+
 # -------------------------------------------------------- A12: sampler ------
 
 def _counts_close(got, want, rtol=0.1):
