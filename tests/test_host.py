@@ -31,7 +31,7 @@ def test_abi_exports_every_declared_symbol():
 
 def test_struct_layout_matches_header():
     assert ctypes.sizeof(_lib.QsvGate) == 4 + 4 + 4 * 12 + 8 + 32
-    assert ctypes.sizeof(_lib.QsvCounters) == 80
+    assert ctypes.sizeof(_lib.QsvCounters) == 96   # 12 uint64 fields of qsv_counters
 
 
 def test_no_device_fails_loudly():
