@@ -235,6 +235,8 @@ int qsv_timer_end(qsv_state* s, float* ms_out);
  *   direct_store, warp_local, fused3, linear_perm, diag_split   k_fused_pass variants
  *   lazy_init, product_init, product_fold  deferred |index>, product-state prologue, prologue folded
  *                                          into the first fused pass
+ *   dist_p2p, dist_fuse_swap, dist_min_lpos  sharded states: peer-memory transport, swap carried by the
+ *                                          next fused pass (k_fused_swap_pass), lowest evictable local bit
  * Environment switches read once per process: QSV_TRACE (per-pass plan + time on stderr),
  * QSV_NO_ZYZ, QSV_NO_LIFT (planner rewrites), QSV_NO_PROB_STORE (basis-change expval keeps amplitudes). */
 int qsv_set_option(qsv_state* s, const char* name, int64_t value);
@@ -243,6 +245,17 @@ int qsv_flush_l2(qsv_state* s);
 /* Host-only view of the single-GPU pass planner (no device work, usable without a GPU): one
  * line per planned pass (kernel kind, tile bits, phases, op counts) is written to `path`. */
 int qsv_debug_plan(int n_qubits, const qsv_gate* gates, uint64_t n_gates, int flags, const char* path);
+
+/* Host-only emulation of the gather arithmetic of the fused swap pass (k_fused_swap_pass: the first
+ * fused pass after a global<->local qubit swap reads its tiles from the peers' slabs): for the first
+ * pass of `gates` on a slab of n_local qubits and the swap (k, lpos[], a = this rank's value on the
+ * swapped global bits) every destination index x gets src_j[x] (source rank as a value of the swapped
+ * global bits), src_addr[x] (local index there) and tile_of[x] (rank-relative tile number);
+ * sig[tile * 16 + i] = ranks tile `tile` signals (0xffffffff: unused); *nin = swapped bits that are
+ * tile bits; *ok = 0 when the first pass is not a fused pass.  No device work (CPU tests). */
+int qsv_debug_fused_swap(int n_local, int k, const int* lpos, int a, const qsv_gate* gates, uint64_t n_gates,
+                         uint32_t* src_j, uint64_t* src_addr, uint32_t* tile_of, uint32_t* sig, int* nin,
+                         int* ok);
 
 /* ---- sharded states (one process per GPU; NCCL over NVLink) -------------- */
 /* 128-byte ncclUniqueId for the bootstrap; rank 0 creates it and the host side

@@ -41,6 +41,18 @@ void qsv_set_error(const char* fmt, ...);
 // ----------------------------------------------------------------- state --
 struct qsv_dist;  // defined in qsv_dist.cu
 
+// A global<->local qubit swap that has been planned (and already applied to `perm`) but not executed:
+// the first fused pass of the next qsv_apply_hgates gathers its tiles from the peers' slabs
+// (k_fused_swap_pass); any other consumer runs the standalone exchange first (qsv_dist_flush_swap).
+struct QsvPendingSwap {
+    int k;
+    int lpos[4];              // local bit paired with swapped global bit i
+    int a;                    // this rank's value on the swapped global bits
+    const double2* peer[16];  // slab of the rank whose swapped global bits read j
+    uint32_t* flag[16];       // that rank's per-tile arrival counters
+    uint32_t* err;            // device error word
+};
+
 struct qsv_state {
     int n;        // total qubits
     int n_local;  // qubits held on this device (n - log2(world))
@@ -98,6 +110,7 @@ struct qsv_state {
     int prod_pending, prod_h;
     double prod_vec[64][4];  // per qubit: (re, im) of the amplitudes of |0> and |1>
     int basis_pending;
+    QsvPendingSwap* pending_swap;  // sharded states: see QsvPendingSwap (owned by qsv_dist)
     int lazy_init;  // option: 0 = qsv_init_basis writes the buffer immediately
     int use_product_init;  // option: product-state prologue in qsv_apply_gates
     int use_product_fold;  // option: the first fused pass generates its tiles from the product tables
@@ -118,6 +131,11 @@ struct HGate {
 };
 // apply gates whose qubits are all local physical bits (qsv_gate.cu)
 int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags);
+
+// sharded states (qsv_dist.cu)
+int qsv_dist_flush_swap(qsv_state* s);                    // run a pending swap as a standalone exchange
+int qsv_dist_fused_swap_begin(qsv_state* s, uint32_t signals_per_tile, uint32_t* target_out);  // barrier + timer start
+int qsv_dist_fused_swap_end(qsv_state* s);                // timer stop, counters, handshake error check
 
 int qsv_materialize(qsv_state* s);  // write a pending |index> into the amplitude buffer
 int qsv_flush_product(qsv_state* s);  // write a pending product state into the amplitude buffer (qsv_gate.cu)

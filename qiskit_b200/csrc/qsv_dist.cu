@@ -90,6 +90,17 @@ struct qsv_dist {
     // device time of the exchanges: event pairs recorded around every swap, folded into
     // ctr.swap_ns when somebody reads the counters (no synchronisation on the hot path)
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timers;
+    // fused swap pass (k_fused_swap_pass, qsv_fused.cuh): per-tile arrival counters of every rank
+    // (own allocation + CUDA-IPC mappings of the peers'), the running value they reach, an error word
+    uint32_t* flags;               // own counters: 2^(n_local - 12) words + 1 error word at the end
+    size_t flag_words;
+    uint32_t* peer_flags[MAX_RANKS];
+    void* ipc_flag_base[MAX_RANKS];
+    uint32_t flag_target;          // identical on every rank: all ranks run the same fused swap passes
+    int use_fuse;                  // option "dist_fuse_swap"
+    QsvPendingSwap pending;        // storage behind qsv_state::pending_swap
+    int pending_gpos[MAX_G], pending_k;
+    cudaEvent_t fused_e0;
 };
 
 void qsv_dist_collect_times(qsv_state* s) {
@@ -110,8 +121,11 @@ void qsv_dist_free(qsv_state* s) {
     if (!d) return;
     cudaStreamSynchronize(s->stream);
     qsv_dist_collect_times(s);
-    for (int r = 0; r < s->world; ++r)
+    for (int r = 0; r < s->world; ++r) {
         if (d->ipc_base[r]) cudaIpcCloseMemHandle(d->ipc_base[r]);
+        if (d->ipc_flag_base[r]) cudaIpcCloseMemHandle(d->ipc_flag_base[r]);
+    }
+    if (d->flags) cudaFree(d->flags);
     if (d->d_tok) cudaFree(d->d_tok);
     if (d->xbuf) cudaFree(d->xbuf);
     if (d->comm) g_nccl.CommDestroy(d->comm);
@@ -193,29 +207,40 @@ extern "C" int qsv_create_dist(qsv_state** out, int n_qubits, int device, int ra
             break;
         }
         cudaMemsetAsync(d->d_tok, 0, 4096, s->stream);
-        // exchange CUDA IPC handles of the slabs through NCCL itself (no other channel needed)
-        cudaIpcMemHandle_t mine;
+        // per-tile arrival counters of the fused swap pass (+ one error word), zeroed once: the counters
+        // only ever grow, every fused swap pass waits for the next multiple
+        d->flag_words = ((size_t)1 << (s->n_local > 12 ? s->n_local - 12 : 0)) + 1;
+        if (cudaMalloc((void**)&d->flags, d->flag_words * sizeof(uint32_t)) != cudaSuccess) {
+            qsv_set_error("cudaMalloc of the fused-swap counters failed");
+            rc = QSV_ERR_NOMEM;
+            break;
+        }
+        cudaMemsetAsync(d->flags, 0, d->flag_words * sizeof(uint32_t), s->stream);
+        d->peer_flags[rank] = d->flags;
+        // exchange CUDA IPC handles of the slabs and the counters through NCCL itself (no other channel needed)
+        cudaIpcMemHandle_t mine[2];
         static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle size");
         d->peer_amp[rank] = s->amp;
         d->p2p = 0;
         const char* env = getenv("QSV_DIST_P2P");
         const int want_p2p = env && *env ? atoi(env) : 1;
-        int ok = want_p2p && cudaIpcGetMemHandle(&mine, s->amp) == cudaSuccess;
+        int ok = want_p2p && cudaIpcGetMemHandle(&mine[0], s->amp) == cudaSuccess &&
+                 cudaIpcGetMemHandle(&mine[1], d->flags) == cudaSuccess;
         if (!ok) {
             cudaGetLastError();
-            memset(&mine, 0, sizeof mine);
+            memset(mine, 0, sizeof mine);
         }
-        char* d_h = (char*)d->d_tok + 64;            // world * 64 bytes of handles, then flags
-        char* d_mine = d_h + MAX_RANKS * 64;
-        cudaMemcpyAsync(d_mine, &mine, 64, cudaMemcpyHostToDevice, s->stream);
-        r = g_nccl.AllGather(d_mine, d_h, 64, ncclChar, d->comm, s->stream);
+        char* d_h = (char*)d->d_tok + 64;            // world * 128 bytes of handles, then this rank's pair
+        char* d_mine = d_h + MAX_RANKS * 128;
+        cudaMemcpyAsync(d_mine, mine, 128, cudaMemcpyHostToDevice, s->stream);
+        r = g_nccl.AllGather(d_mine, d_h, 128, ncclChar, d->comm, s->stream);
         if (r != ncclSuccess) {
             qsv_set_error("ncclAllGather of IPC handles failed: %s", g_nccl.GetErrorString(r));
             rc = QSV_ERR_NCCL;
             break;
         }
-        cudaIpcMemHandle_t all[MAX_RANKS];
-        cudaMemcpyAsync(all, d_h, 64 * world, cudaMemcpyDeviceToHost, s->stream);
+        cudaIpcMemHandle_t all[MAX_RANKS][2];
+        cudaMemcpyAsync(all, d_h, 128 * world, cudaMemcpyDeviceToHost, s->stream);
         if (cudaStreamSynchronize(s->stream) != cudaSuccess) {
             qsv_set_error("sharded setup: stream failed: %s", cudaGetErrorString(cudaGetLastError()));
             rc = QSV_ERR_CUDA;
@@ -225,13 +250,21 @@ extern "C" int qsv_create_dist(qsv_state** out, int n_qubits, int device, int ra
             for (int p = 0; p < world && ok; ++p) {
                 if (p == rank) continue;
                 void* base = nullptr;
-                if (cudaIpcOpenMemHandle(&base, all[p], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                if (cudaIpcOpenMemHandle(&base, all[p][0], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
                     cudaGetLastError();
                     ok = 0;
                     break;
                 }
                 d->ipc_base[p] = base;
                 d->peer_amp[p] = (double2*)base;
+                base = nullptr;
+                if (cudaIpcOpenMemHandle(&base, all[p][1], cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) {
+                    cudaGetLastError();
+                    ok = 0;
+                    break;
+                }
+                d->ipc_flag_base[p] = base;
+                d->peer_flags[p] = (uint32_t*)base;
             }
         }
         // every rank must take the same transport: min over ranks of `ok`
@@ -247,6 +280,8 @@ extern "C" int qsv_create_dist(qsv_state** out, int n_qubits, int device, int ra
         cudaStreamSynchronize(s->stream);
         d->p2p = flag > 0.5;
         d->use_p2p = d->p2p;
+        const char* fenv = getenv("QSV_DIST_FUSE_SWAP");
+        d->use_fuse = d->p2p && (fenv && *fenv ? atoi(fenv) : 1);
     } while (0);
     if (rc != QSV_OK) {
         std::string msg = qsv_last_error();
@@ -272,6 +307,11 @@ int qsv_dist_set_option(qsv_state* s, const char* name, int64_t value) {
     if (!strcmp(name, "dist_p2p")) {
         if (value && !s->dist->p2p) QSV_FAIL(QSV_ERR_UNSUPPORTED, "peer slabs are not mapped (CUDA IPC unavailable)");
         s->dist->use_p2p = value != 0;
+        return QSV_OK;
+    }
+    if (!strcmp(name, "dist_fuse_swap")) {
+        if (value && !s->dist->p2p) QSV_FAIL(QSV_ERR_UNSUPPORTED, "peer slabs are not mapped (CUDA IPC unavailable)");
+        s->dist->use_fuse = value != 0;
         return QSV_OK;
     }
     if (!strcmp(name, "dist_min_lpos")) {
@@ -361,14 +401,12 @@ __global__ void __launch_bounds__(256) k_swap_unpack(double2* __restrict__ mine,
 }
 
 // Exchange physical global bits gpos[i] (>= n_local) with physical local bits lpos[i], i < k.
-static int dist_swap_bits(qsv_state* s, int k, const int* gpos, const int* lpos) {
+static int swap_args(qsv_state* s, int k, const int* gpos, const int* lpos, SwapArgs& A, int* peers_rank) {
     qsv_dist* d = s->dist;
     if (k < 1 || k > d->g) QSV_FAIL(QSV_ERR_INVALID, "internal: swap of %d bits", k);
-    SwapArgs A;
     memset(&A, 0, sizeof A);
     A.k = k;
     A.rest = 1ull << (s->n_local - k);
-    int peers_rank[1 << MAX_G];
     for (int i = 0; i < k; ++i) {
         A.lpos[i] = lpos[i];
         A.lsorted[i] = lpos[i];
@@ -384,6 +422,25 @@ static int dist_swap_bits(qsv_state* s, int k, const int* gpos, const int* lpos)
         peers_rank[j] = r;
         A.peer[j] = d->peer_amp[r];
     }
+    return QSV_OK;
+}
+
+// the logical qubits that sit on those physical bits trade places
+static void swap_commit_perm(qsv_state* s, int k, const int* gpos, const int* lpos) {
+    for (int q = 0; q < s->n; ++q) {
+        for (int i = 0; i < k; ++i) {
+            if (s->perm[q] == gpos[i]) { s->perm[q] = lpos[i]; break; }
+            if (s->perm[q] == lpos[i]) { s->perm[q] = gpos[i]; break; }
+        }
+    }
+}
+
+// the standalone exchange (data movement only; perm is the caller's business)
+static int swap_execute(qsv_state* s, int k, const int* gpos, const int* lpos) {
+    qsv_dist* d = s->dist;
+    SwapArgs A;
+    int peers_rank[1 << MAX_G];
+    QSV_TRY(swap_args(s, k, gpos, lpos, A, peers_rank));
     const int npeers = (1 << k) - 1;
     static const bool trace = getenv("QSV_TRACE") != nullptr;
     cudaEvent_t te0 = nullptr, te1 = nullptr;
@@ -448,13 +505,88 @@ static int dist_swap_bits(qsv_state* s, int k, const int* gpos, const int* lpos)
     }
     s->ctr.swap_count++;
     s->ctr.swap_bytes += (uint64_t)npeers * A.rest * 16;
-    // the logical qubits that sat on those physical bits trade places
-    for (int q = 0; q < s->n; ++q) {
-        for (int i = 0; i < k; ++i) {
-            if (s->perm[q] == gpos[i]) { s->perm[q] = lpos[i]; break; }
-            if (s->perm[q] == lpos[i]) { s->perm[q] = gpos[i]; break; }
-        }
+    return QSV_OK;
+}
+
+static int dist_swap_bits(qsv_state* s, int k, const int* gpos, const int* lpos) {
+    QSV_TRY(swap_execute(s, k, gpos, lpos));
+    swap_commit_perm(s, k, gpos, lpos);
+    return QSV_OK;
+}
+
+// ---- fused swap pass plumbing (the kernel and its descriptors live in qsv_fused.cuh / qsv_gate.cu) ----
+// Plan the swap, update perm, and leave the data movement to the first fused pass that follows.
+static int swap_defer(qsv_state* s, int k, const int* gpos, const int* lpos) {
+    qsv_dist* d = s->dist;
+    SwapArgs A;
+    int peers_rank[1 << MAX_G];
+    QSV_TRY(swap_args(s, k, gpos, lpos, A, peers_rank));
+    QsvPendingSwap& W = d->pending;
+    memset(&W, 0, sizeof W);
+    W.k = k;
+    W.a = A.a;
+    for (int i = 0; i < k; ++i) {
+        W.lpos[i] = lpos[i];
+        d->pending_gpos[i] = gpos[i];
     }
+    d->pending_k = k;
+    for (int j = 0; j < (1 << k); ++j) {
+        W.peer[j] = d->peer_amp[peers_rank[j]];
+        W.flag[j] = d->peer_flags[peers_rank[j]];
+    }
+    W.err = d->flags + (d->flag_words - 1);
+    swap_commit_perm(s, k, gpos, lpos);
+    s->pending_swap = &W;
+    return QSV_OK;
+}
+
+// nobody could carry the pending swap: run it as the standalone exchange (perm is already updated,
+// the data is not -- the kernel only needs the bit positions)
+int qsv_dist_flush_swap(qsv_state* s) {
+    qsv_dist* d = s->dist;
+    if (!d || !s->pending_swap) return QSV_OK;
+    s->pending_swap = nullptr;
+    return swap_execute(s, d->pending_k, d->pending_gpos, d->pending.lpos);
+}
+
+int qsv_dist_fused_swap_begin(qsv_state* s, uint32_t signals_per_tile, uint32_t* target_out) {
+    qsv_dist* d = s->dist;
+    if (!d || !s->pending_swap) QSV_FAIL(QSV_ERR_INVALID, "internal: no pending swap");
+    d->flag_target += signals_per_tile;
+    *target_out = d->flag_target;
+    cudaEvent_t e0 = nullptr;
+    QSV_CUDA(cudaEventCreate(&e0));
+    QSV_CUDA(cudaEventRecord(e0, s->stream));
+    d->fused_e0 = e0;
+    // every rank's earlier work on its slab must be complete before anybody gathers from it
+    return dist_barrier(s);
+}
+
+int qsv_dist_fused_swap_end(qsv_state* s) {
+    qsv_dist* d = s->dist;
+    cudaEvent_t e1 = nullptr;
+    QSV_CUDA(cudaEventCreate(&e1));
+    QSV_CUDA(cudaEventRecord(e1, s->stream));
+    d->timers.emplace_back(d->fused_e0, e1);
+    const int k = d->pending_k;
+    const uint64_t npeers = (1ull << k) - 1;
+    s->ctr.swap_count++;
+    s->ctr.fused_swaps++;
+    s->ctr.swap_bytes += npeers * (16ull << (s->n_local - k));
+    // a handshake that timed out leaves wrong amplitudes behind: find out now (one word, one sync per swap)
+    QSV_TRY(qsv_ensure_pinned(s, 64));
+    uint32_t* h = (uint32_t*)s->pinned + 8;
+    QSV_CUDA(cudaMemcpyAsync(h, d->flags + (d->flag_words - 1), sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
+    QSV_CUDA(cudaStreamSynchronize(s->stream));
+    static const bool trace = getenv("QSV_TRACE") != nullptr;
+    if (trace && s->rank == 0) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, d->fused_e0, e1);
+        const double gb = (double)npeers * (16ull << (s->n_local - k)) / 1e9;
+        fprintf(stderr, "[fused swap pass] k=%d gathered %.2f GB/rank in %.3f ms = %.1f GB/s per direction\n", k, gb, ms,
+                gb / (ms / 1e3));
+    }
+    if (*h) QSV_FAIL(QSV_ERR_NCCL, "fused swap pass: a peer did not arrive in time (handshake timeout)");
     return QSV_OK;
 }
 
@@ -617,9 +749,31 @@ int qsv_dist_apply(qsv_state* s, std::vector<HGate>& gates, int flags) {
     std::vector<PlanStep> steps;
     QSV_TRY(dist_plan(s->n, s->n_local, s->perm, pg, d->min_lpos, steps));
     cplx scalar(1.0, 0.0);
-    for (const PlanStep& st : steps) {
+    for (size_t si = 0; si < steps.size(); ++si) {
+        const PlanStep& st = steps[si];
         if (st.kind == 1) {
-            QSV_TRY(dist_do_swap(s, st));
+            // Fused swap pass: when every gate of the following run is fully local after the swap, all
+            // ranks hold the same gate list, plan the same passes, and the first fused pass can gather its
+            // tiles from the peers (qsv_gate.cu takes it from there, or falls back to the standalone kernel)
+            bool defer = d->use_fuse && d->use_p2p && !(flags & QSV_FLAG_NO_FUSION) && si + 1 < steps.size() &&
+                         steps[si + 1].kind == 0 && s->n_local >= 12;
+            if (defer) {
+                int perm2[64];
+                memcpy(perm2, s->perm, sizeof perm2);
+                for (int i = 0; i < st.k; ++i) std::swap(perm2[st.gin[i]], perm2[st.lout[i]]);
+                for (int id : steps[si + 1].gates)
+                    for (int j = 0; j < gates[id].k && defer; ++j) defer = perm2[gates[id].q[j]] < s->n_local;
+            }
+            if (defer) {
+                int gpos[MAX_G], lpos[MAX_G];
+                for (int i = 0; i < st.k; ++i) {
+                    gpos[i] = s->perm[st.gin[i]];
+                    lpos[i] = s->perm[st.lout[i]];
+                }
+                QSV_TRY(swap_defer(s, st.k, gpos, lpos));
+            } else {
+                QSV_TRY(dist_do_swap(s, st));
+            }
             continue;
         }
         std::vector<HGate> local;
@@ -657,12 +811,16 @@ int qsv_dist_apply(qsv_state* s, std::vector<HGate>& gates, int flags) {
             }
             if (!ident) local.push_back(std::move(h));
         }
-        if (scalar != cplx(1.0, 0.0) && !local.empty()) {
+        // a rank-dependent scalar must not change what the planner sees while a swap is pending
+        // (every rank has to cut the same passes): it waits for the next run or the final qsv_scale
+        if (scalar != cplx(1.0, 0.0) && !local.empty() && !s->pending_swap) {
             for (cplx& v : local[0].m) v *= scalar;
             scalar = cplx(1.0, 0.0);
         }
         if (!local.empty()) QSV_TRY(qsv_apply_hgates(s, local, flags));
+        else if (s->pending_swap) QSV_TRY(qsv_dist_flush_swap(s));
     }
+    if (s->pending_swap) QSV_TRY(qsv_dist_flush_swap(s));
     if (scalar != cplx(1.0, 0.0)) QSV_TRY(qsv_scale(s, scalar.real(), scalar.imag()));
     return QSV_OK;
 }

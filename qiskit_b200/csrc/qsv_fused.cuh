@@ -101,6 +101,76 @@ __host__ __device__ __forceinline__ uint32_t fp_swz(uint32_t i) {
     return i ^ (((i >> 3) ^ (i >> 6) ^ (i >> 9)) & 7u);
 }
 
+// ---- fused swap pass: a global<->local qubit swap riding inside the copy-in of a fused pass ------
+//
+// Sharded states (qsv_dist.cu).  Swapping k global bits with the local bits lpos[0..k) means: the
+// amplitude that ends up at local index x of this rank (swapped global bits = a) sits, before the
+// swap, on the rank whose swapped global bits equal the bits of x at lpos[] (call that value j), at
+// the local index x with those bits replaced by a.  Instead of moving the data first and sweeping
+// it again, the first fused pass after the swap gathers its tiles straight from the peers' slabs
+// (CUDA-IPC mappings, NVLink) and stores them -- in place -- into its own slab.
+//
+// In place across ranks needs an ordering: the region a tile of rank a overwrites is exactly what the
+// matching tiles of the ranks it read from are reading.  "Matching" tiles carry the same tile NUMBER
+// on every rank because tiles are enumerated relative to the rank: the swapped local bits that are
+// not tile bits are XORed with the rank's own bits (out_xor).  Every CTA therefore (1) waits for its
+// tile to land, (2) adds 1 to the arrival counter of that tile number on every rank it read from,
+// (3) computes, (4) spins until its own counter for the tile has reached `target` (all readers of its
+// region have their data), (5) stores.  All ranks launch the same grid over the same tile numbers, all
+// CTAs of the grid are resident (2 per SM), a CTA signals tile i before it waits for tile i, and loads
+// never wait: no cycle.  A clock64 timeout turns a would-be hang into an error word.
+#define FPR_MAXK 4
+struct FpRemote {
+    const double2* peer[1 << FPR_MAXK];  // slab of the rank whose swapped global bits read j (peer[a]: own)
+    uint32_t* flag[1 << FPR_MAXK];       // arrival counters (one per tile number) of that rank
+    uint32_t* err;                       // set to 1 when a handshake times out
+    uint32_t target;                     // value every counter of this rank reaches during this pass
+    int32_t a;                           // this rank's value on the swapped global bits
+    int32_t k, nin, nout;
+    uint8_t in_j[FPR_MAXK];              // swapped local bits that are tile bits: their bit in j
+    uint8_t out_j[FPR_MAXK];             // swapped local bits that are not: their bit in j ...
+    uint8_t out_pos[FPR_MAXK];           // ... and their position in the local index
+    int8_t thr_bit[FPR_MAXK];            // [i]: copy-in thread bit (0..7) carrying swapped local bit i, or -1
+    uint8_t jrow[16];                    // bits of j contributed by tile row r
+    uint64_t row_clean[16];              // byte offset of tile row r with the swapped bits cleared
+    uint64_t lmask;                      // local-index mask of the swapped local bits
+    uint64_t a_l;                        // a scattered to those positions
+    uint64_t out_xor;                    // a's bits at the non-tile swapped positions (relative tile order)
+    long long timeout;                   // clock64 ticks a CTA waits before it reports an error
+};
+
+__host__ __device__ __forceinline__ uint64_t fp_tile_base(const FpPass& P, uint32_t tile) {
+    uint64_t base = 0;
+    for (int sgm = 0; sgm < P.nseg; ++sgm)
+        base |= (uint64_t)((tile >> P.seg_src[sgm]) & P.seg_mask[sgm]) << P.seg_dst[sgm];
+    return base;
+}
+// bits of j fixed by the tile (swapped local bits outside the tile)
+__host__ __device__ __forceinline__ uint32_t fpr_j_tile(const FpRemote& R, uint64_t tile_base) {
+    uint32_t j = 0;
+    for (int i = 0; i < R.nout; ++i) j |= (uint32_t)((tile_base >> R.out_pos[i]) & 1ull) << R.out_j[i];
+    return j;
+}
+// bits of j carried by copy-in thread t
+__host__ __device__ __forceinline__ uint32_t fpr_j_thread(const FpRemote& R, uint32_t t) {
+    uint32_t j = 0;
+    for (int i = 0; i < R.k; ++i)
+        if (R.thr_bit[i] >= 0) j |= ((t >> R.thr_bit[i]) & 1u) << i;
+    return j;
+}
+// copy-in thread offset (elements) of thread t: tile bits 0..7 scattered to their index positions
+__host__ __device__ __forceinline__ uint64_t fp_cp_off(const FpPass& P, uint32_t t) {
+    uint64_t o = 0;
+    for (int b = 0; b < 8; ++b) o |= (uint64_t)((t >> b) & 1u) << P.pos[b];
+    return o;
+}
+// rank (as a value j of the swapped global bits) signalled by lane x of a tile's 2^nin signals
+__host__ __device__ __forceinline__ uint32_t fpr_signal_peer(const FpRemote& R, uint32_t j_tile, uint32_t x) {
+    uint32_t j = j_tile;
+    for (int b = 0; b < R.nin; ++b) j |= ((x >> b) & 1u) << R.in_j[b];
+    return j;
+}
+
 // ---- dense ops on the 16 registers of a thread, in place --------------------------------
 template <int B>
 __device__ __forceinline__ void fp_d1c(double2 (&v)[16], const FpPass& P, int mo) {
@@ -318,13 +388,30 @@ __device__ __forceinline__ void fp_apply(double2 (&v)[16], const FpPass& P, int 
     }
 }
 
+// spin until this rank's arrival counter of tile `tile` has reached the pass's target
+__device__ __forceinline__ void fpr_wait(const FpRemote& R, uint32_t tile) {
+    const volatile uint32_t* f = R.flag[R.a] + tile;
+    const long long t0 = clock64();
+    uint32_t spins = 0;
+    while (true) {
+        uint32_t v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(f) : "memory");
+        if ((int32_t)(v - R.target) >= 0) break;
+        if ((++spins & 63u) == 0 && (*reinterpret_cast<const volatile uint32_t*>(R.err) || clock64() - t0 > R.timeout)) {
+            atomicExch(R.err, 1u);  // one late CTA is enough: everybody else stops waiting too
+            break;
+        }
+    }
+}
+
 // dynamic smem: [4096] double2 tile buffer, then [ntabs][256] u16 tables.  Two CTAs per SM: while
 // one waits for its tile or at a barrier the other computes; in a direct-store last phase the
 // buffer is free as soon as every thread has read its registers, so the next tile's cp.async
 // copies are issued before that phase's arithmetic.
 // `src` = `amp` for the usual in-place pass; a different `src` makes the pass out of place (tiles are
 // read from src and written to amp), which saves the scratch copy of basis-change expectation values.
-__global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const double2* src, const __grid_constant__ FpPass P) {
+template <bool REMOTE>
+__device__ __forceinline__ void fp_pass_body(double2* amp, const double2* src, const FpPass& P, const FpRemote& R) {
     extern __shared__ __align__(16) unsigned char fp_smem[];
     unsigned char* const tilebuf = fp_smem;
     uint16_t* const tabs_sm = reinterpret_cast<uint16_t*>(fp_smem + FP_TILE * sizeof(double2));
@@ -342,16 +429,26 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const dou
     uint64_t st_thread = 0;
 #pragma unroll
     for (int b = 0; b < 8; ++b) st_thread |= (uint64_t)((t >> b) & 1u) << P.pos[P.st_tpos[b]];
+    // fused swap pass: this thread's share of the source-rank selector and its cleaned offset
+    const uint32_t rj_thr = REMOTE ? fpr_j_thread(R, t) : 0u;
+    const uint64_t rcp_clean = REMOTE ? (cp_off & ~R.lmask) : 0ull;
 
     auto tile_base_of = [&](uint32_t tile) {
-        uint64_t base = 0;
-        for (int sgm = 0; sgm < P.nseg; ++sgm)
-            base |= (uint64_t)((tile >> P.seg_src[sgm]) & P.seg_mask[sgm]) << P.seg_dst[sgm];
-        return base;
+        const uint64_t base = fp_tile_base(P, tile);
+        return REMOTE ? (base ^ R.out_xor) : base;
     };
     auto issue_load = [&](uint64_t tile_base) {
         const uint32_t dst0 = (uint32_t)__cvta_generic_to_shared(tilebuf);
-        if (P.gen_h > 0) {
+        if (REMOTE) {
+            const uint32_t jt = fpr_j_tile(R, tile_base) | rj_thr;
+            const uint64_t off = ((tile_base & ~R.lmask) | R.a_l) + rcp_clean;
+#pragma unroll
+            for (int r = 0; r < 16; ++r) {
+                const uint32_t dst = dst0 + (st16 ^ (fp_swz((uint32_t)r << 8) << 4));
+                const char* g = reinterpret_cast<const char*>(R.peer[jt | R.jrow[r]] + off) + R.row_clean[r];
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(g));
+            }
+        } else if (P.gen_h > 0) {
             const char* g = reinterpret_cast<const char*>(P.gen_tile + t);
 #pragma unroll
             for (int r = 0; r < 16; ++r) {
@@ -376,11 +473,16 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const dou
     while (true) {
         asm volatile("cp.async.wait_group 0;\n" ::: "memory");
         __syncthreads();  // tile (and, first time, the tables) visible to every thread
+        if (REMOTE && t < (1u << R.nin)) {
+            // every load of this CTA has landed: tell the ranks it read from (their tile `tile`)
+            __threadfence_system();
+            atomicAdd_system(R.flag[fpr_signal_peer(R, fpr_j_tile(R, tile_base), t)] + tile, 1u);
+        }
         const uint32_t next = tile + gridDim.x;
         const bool has_next = next < P.ntiles;
         const uint64_t next_base = has_next ? tile_base_of(next) : 0;
         const uint64_t diag_base = tile_base | P.index_base;
-        if (P.gen_h > 0 && has_next) {  // the next tile's two table entries: into L1 ahead of their use
+        if (!REMOTE && P.gen_h > 0 && has_next) {  // the next tile's two table entries: into L1 ahead of their use
             asm volatile("prefetch.global.L1 [%0];\n" ::"l"(P.gen_lo + (next_base & ((1ull << P.gen_h) - 1))));
             asm volatile("prefetch.global.L1 [%0];\n" ::"l"(P.gen_hi + (next_base >> P.gen_h)));
         }
@@ -390,7 +492,7 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const dou
             const FpPhase& ph = P.phases[p];
             const uint32_t sb = (uint32_t)tabs_sm[ph.tab * FP_NT + t] << 4;
             double2 v[16];
-            if (P.gen_h > 0 && p == 0) {
+            if (!REMOTE && P.gen_h > 0 && p == 0) {
                 const double2 cb = cmul(__ldg(P.gen_lo + (tile_base & ((1ull << P.gen_h) - 1))),
                                         __ldg(P.gen_hi + (tile_base >> P.gen_h)));
 #pragma unroll
@@ -402,6 +504,7 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const dou
             }
             if (ph.direct) {
                 // every thread has its registers: the buffer can take the next tile now
+                if (REMOTE && t == 0) fpr_wait(R, tile);  // ... and the peers have read what this tile overwrites
                 __syncthreads();
                 if (has_next) issue_load(next_base);
             }
@@ -420,7 +523,7 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const dou
             }
             if (ph.direct) {
                 char* g = reinterpret_cast<char*>(amp + tile_base + st_thread);
-                if (P.store_prob) {
+                if (!REMOTE && P.store_prob) {
                     g -= (st_thread & 15ull) << 3;
 #pragma unroll
                     for (int r = 0; r < 16; ++r)
@@ -439,6 +542,10 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const dou
             }
         }
         if (!stored) {
+            if (REMOTE) {
+                if (t == 0) fpr_wait(R, tile);
+                __syncthreads();
+            }
             const uint32_t so16 = P.out_tab == 0xffff ? st16 : ((uint32_t)tabs_sm[P.out_tab * FP_NT + t] << 4);
             char* g = reinterpret_cast<char*>(amp + tile_base + cp_off);
 #pragma unroll
@@ -452,6 +559,16 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const dou
         tile = next;
         tile_base = next_base;
     }
+}
+
+__global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const double2* src, const __grid_constant__ FpPass P) {
+    fp_pass_body<false>(amp, src, P, *reinterpret_cast<const FpRemote*>(&P));  // R is never read
+}
+
+// the same pass with its tiles gathered from the peers' slabs (see FpRemote)
+__global__ void __launch_bounds__(FP_NT, 2) k_fused_swap_pass(double2* amp, const __grid_constant__ FpPass P,
+                                                              const __grid_constant__ FpRemote R) {
+    fp_pass_body<true>(amp, amp, P, R);
 }
 
 // ---- k_fused_pass3: the same pass with THREE tile buffers per SM --------------------------------

@@ -2147,8 +2147,93 @@ static void trace_fused_pass(const FpPass& P, FILE* f) {
 
 static int upload_product_tables(qsv_state* s, uint64_t neutral, const std::vector<cplx>& extra);
 
+// Descriptor of the remote gather of a fused swap pass: where the swapped local bits sit relative to
+// the pass's tile (row bits, copy-in thread bits, or outside the tile), see FpRemote in qsv_fused.cuh.
+static void build_fp_remote(const FpPass& P, const QsvPendingSwap& W, FpRemote& R) {
+    memset(&R, 0, sizeof R);
+    R.k = W.k;
+    R.a = W.a;
+    R.err = W.err;
+    for (int j = 0; j < (1 << W.k); ++j) {
+        R.peer[j] = W.peer[j];
+        R.flag[j] = W.flag[j];
+    }
+    int tile_bit_of[64];
+    for (int b = 0; b < 64; ++b) tile_bit_of[b] = -1;
+    for (int b = 0; b < FP_T; ++b) tile_bit_of[P.pos[b]] = b;
+    for (int i = 0; i < W.k; ++i) {
+        const int lp = W.lpos[i];
+        const uint64_t abit = (uint64_t)((W.a >> i) & 1);
+        R.lmask |= 1ull << lp;
+        R.a_l |= abit << lp;
+        R.thr_bit[i] = -1;
+        const int tb = tile_bit_of[lp];
+        if (tb < 0) {
+            R.out_j[R.nout] = (uint8_t)i;
+            R.out_pos[R.nout] = (uint8_t)lp;
+            ++R.nout;
+            R.out_xor |= abit << lp;
+        } else {
+            R.in_j[R.nin++] = (uint8_t)i;
+            if (tb < 8) R.thr_bit[i] = (int8_t)tb;
+        }
+    }
+    for (int r = 0; r < 16; ++r) {
+        uint32_t jr = 0;
+        uint64_t clean = 0;
+        for (int jb = 0; jb < 4; ++jb) {
+            if (!((r >> jb) & 1)) continue;
+            const int pos = P.pos[8 + jb];
+            int which = -1;
+            for (int i = 0; i < W.k; ++i)
+                if (W.lpos[i] == pos) which = i;
+            if (which >= 0) jr |= 1u << which;
+            else clean |= 1ull << pos;
+        }
+        R.jrow[r] = (uint8_t)jr;
+        R.row_clean[r] = clean * sizeof(double2);
+    }
+    static const long long to_ms = getenv("QSV_FUSED_SWAP_TIMEOUT_MS") ? atoll(getenv("QSV_FUSED_SWAP_TIMEOUT_MS")) : 4000;
+    R.timeout = to_ms * 2000000ll;  // ~2 GHz SM clock
+}
+
+// a fused pass can carry the pending swap when it reads its own buffer in the plain way
+static bool fused_swap_capable(const qsv_state* s, const FpPass& P) {
+    return s->pending_swap && !s->read_from && !s->prod_pending && !P.store_prob && !s->use_fused3;
+}
+
+static int launch_fused_swap_pass(qsv_state* s, const FpPass& P) {
+    const size_t smem = FP_TILE * sizeof(double2) + (size_t)P.ntabs * FP_NT * sizeof(uint16_t);
+    static bool attr_set = false;
+    if (!attr_set) {
+        QSV_CUDA(cudaFuncSetAttribute(k_fused_swap_pass, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)(FP_TILE * sizeof(double2) + FP_MAX_TABS * FP_NT * sizeof(uint16_t))));
+        attr_set = true;
+    }
+    FpRemote R;
+    build_fp_remote(P, *s->pending_swap, R);
+    static const bool trace = getenv("QSV_TRACE") != nullptr;
+    if (trace) {
+        trace_fused_pass(P, stderr);
+        fprintf(stderr, "        (fused swap pass: k=%d, %d of the swapped bits are tile bits, tiles gathered over NVLink)\n",
+                R.k, R.nin);
+    }
+    QSV_TRY(qsv_dist_fused_swap_begin(s, 1u << R.nin, &R.target));
+    const unsigned grid = (unsigned)std::min<uint64_t>(P.ntiles, (uint64_t)s->num_sms * 2);
+    k_fused_swap_pass<<<grid, FP_NT, smem, s->stream>>>(s->amp, P, R);
+    QSV_CUDA(cudaGetLastError());
+    s->pending_swap = nullptr;
+    s->ctr.kernel_launches++;
+    s->ctr.state_passes++;
+    return qsv_dist_fused_swap_end(s);
+}
+
 static int launch_fused_pass(qsv_state* s, const FusedBuilt& fb) {
     const FpPass& P = fb.P;
+    if (s->pending_swap) {
+        if (fused_swap_capable(s, P)) return launch_fused_swap_pass(s, P);
+        QSV_TRY(qsv_dist_flush_swap(s));
+    }
     const size_t smem = FP_TILE * sizeof(double2) + (size_t)P.ntabs * FP_NT * sizeof(uint16_t);
     static bool attr_set = false;
     if (!attr_set) {
@@ -2266,6 +2351,8 @@ static bool tile_capable(const HGate& g) {
 
 // Apply classified gates whose qubits are all local (physical bits < n_local).
 static thread_local FILE* g_plan_dump = nullptr;
+static thread_local FpPass* g_capture_first = nullptr;   // qsv_debug_fused_swap: copy of the first fused pass
+static thread_local int g_capture_state = 0;             // 0 nothing seen, 1 captured, 2 first pass is not a fused pass
 
 int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
     const bool no_fusion = flags & QSV_FLAG_NO_FUSION;
@@ -2314,6 +2401,14 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
                 }
             }
             if (g_plan_dump) {  // host-only planning (qsv_debug_plan): report and skip the device work
+                if (g_capture_first && g_capture_state == 0 && !passes.empty()) {
+                    if (kind[0] == 3) {
+                        *g_capture_first = fparams[0].P;
+                        g_capture_state = 1;
+                    } else {
+                        g_capture_state = 2;
+                    }
+                }
                 for (size_t i = 0; i < passes.size(); ++i) {
                     fprintf(g_plan_dump, "pass kind=%d gates=%zu ", (int)kind[i], passes[i].gate_ids.size());
                     if (kind[i] == 3) trace_fused_pass(fparams[i].P, g_plan_dump);
@@ -2337,6 +2432,7 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
                 s->ctr.h2d_bytes += used;
             }
             if (!passes.empty() && kind[0] != 3) QSV_TRY(qsv_flush_product(s));
+            if (s->pending_swap && (passes.empty() || kind[0] != 3)) QSV_TRY(qsv_dist_flush_swap(s));
             if (s->read_from && kind[0] != 3) {  // out-of-place request, but the first pass cannot do it
                 QSV_CUDA(cudaMemcpyAsync(s->amp, s->read_from, (size_t)16 << s->n_local, cudaMemcpyDeviceToDevice,
                                          s->stream));
@@ -2372,6 +2468,7 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
         }
         if (end < gates.size()) {
             QSV_TRY(qsv_flush_product(s));
+            if (s->pending_swap) QSV_TRY(qsv_dist_flush_swap(s));
             if (s->read_from) {
                 QSV_CUDA(cudaMemcpyAsync(s->amp, s->read_from, (size_t)16 << s->n_local, cudaMemcpyDeviceToDevice,
                                          s->stream));
@@ -2383,6 +2480,7 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
         }
         start = end;
     }
+    if (s->pending_swap) QSV_TRY(qsv_dist_flush_swap(s));  // nothing consumed it (empty stream)
     return QSV_OK;
 }
 
@@ -2636,4 +2734,74 @@ extern "C" int qsv_apply_diagonal(qsv_state* s, const double* diag, int k, const
     for (int i = 0; i < k; ++i) g.qargs[i] = qargs[i];
     g.data = diag;
     return qsv_apply_gates(s, &g, 1, 0);
+}
+
+// Host-only emulation of the address arithmetic of k_fused_swap_pass (tests/test_host.py): for the
+// first fused pass of `gates` on a slab of n_local qubits and a pending swap (k, lpos, a), every
+// destination index x of this rank gets the source it is gathered from -- src_j[x] (value of the
+// swapped global bits of the source rank) and src_addr[x] (local index there) -- and tile_of[x], the
+// RELATIVE tile number that owns x; sig[tile * 16 + i] lists the ranks (as j values) tile `tile`
+// signals (0xffffffff = unused).  Uses the same FpPass / FpRemote builders and the same
+// __host__ __device__ helpers as the kernel.  *ok = 0 when the first pass is not a fused pass.
+extern "C" int qsv_debug_fused_swap(int n_local, int k, const int* lpos, int a, const qsv_gate* gates, uint64_t n_gates,
+                                    uint32_t* src_j, uint64_t* src_addr, uint32_t* tile_of, uint32_t* sig,
+                                    int* nin_out, int* ok) {
+    if (n_local < FP_T || n_local > 30 || k < 1 || k > FPR_MAXK || !lpos || !src_j || !src_addr || !tile_of || !sig || !ok)
+        QSV_FAIL(QSV_ERR_INVALID, "qsv_debug_fused_swap: bad argument");
+    qsv_state st;
+    memset(&st, 0, sizeof st);
+    st.n = st.n_local = n_local;
+    st.world = 1;
+    st.num_sms = 148;
+    for (int q = 0; q < 64; ++q) st.perm[q] = q;
+    qsv_state_defaults(&st);
+    FILE* f = fopen("/dev/null", "w");
+    if (!f) QSV_FAIL(QSV_ERR_INVALID, "qsv_debug_fused_swap: cannot open /dev/null");
+    FpPass* P = new FpPass();
+    g_plan_dump = f;
+    g_capture_first = P;
+    g_capture_state = 0;
+    cudaSetDevice(0);
+    cudaGetLastError();
+    int rc = qsv_apply_gates_impl(&st, gates, n_gates, 0);
+    g_plan_dump = nullptr;
+    g_capture_first = nullptr;
+    fclose(f);
+    *ok = (rc == QSV_OK && g_capture_state == 1) ? 1 : 0;
+    if (!*ok) {
+        delete P;
+        return rc;
+    }
+    QsvPendingSwap W;
+    memset(&W, 0, sizeof W);
+    W.k = k;
+    W.a = a;
+    for (int i = 0; i < k; ++i) W.lpos[i] = lpos[i];
+    FpRemote R;
+    build_fp_remote(*P, W, R);
+    if (nin_out) *nin_out = R.nin;
+    const uint64_t count = 1ull << n_local;
+    for (uint64_t x = 0; x < count; ++x) tile_of[x] = 0xffffffffu;
+    for (uint32_t tile = 0; tile < P->ntiles; ++tile) {
+        const uint64_t base = fp_tile_base(*P, tile) ^ R.out_xor;
+        const uint32_t jt = fpr_j_tile(R, base);
+        for (uint32_t x = 0; x < 16; ++x) sig[(size_t)tile * 16 + x] = x < (1u << R.nin) ? fpr_signal_peer(R, jt, x) : 0xffffffffu;
+        for (uint32_t t = 0; t < FP_NT; ++t) {
+            const uint64_t cp = fp_cp_off(*P, t);
+            const uint32_t jth = fpr_j_thread(R, t);
+            for (int r = 0; r < 16; ++r) {
+                const uint64_t dest = base + cp + P->row_off[r] / sizeof(double2);
+                if (dest >= count || tile_of[dest] != 0xffffffffu) {
+                    delete P;
+                    QSV_FAIL(QSV_ERR_INVALID, "qsv_debug_fused_swap: destination %llu covered twice or out of range",
+                             (unsigned long long)dest);
+                }
+                tile_of[dest] = tile;
+                src_j[dest] = jt | jth | R.jrow[r];
+                src_addr[dest] = ((base & ~R.lmask) | R.a_l) + (cp & ~R.lmask) + R.row_clean[r] / sizeof(double2);
+            }
+        }
+    }
+    delete P;
+    return QSV_OK;
 }

@@ -29,11 +29,18 @@ def main():
     cases.append(("qv16", 16, lib.quantum_volume(16, 6, seed=5)))
     cases.append(("tfim17", 17, lib.named_to_matrices(lib.tfim_named(17, steps=3))))
     cases.append(("qft15", 15, lib.named_to_matrices(lib.qft_named(15))))
-    for transport in (1, 0):
+    cases.append(("qv20", 20, lib.quantum_volume(20, 8, seed=9)))      # several swaps ride inside fused passes
+    cases.append(("su2_19", 19, lib.named_to_matrices(lib.efficient_su2_named(
+        19, 2, np.random.default_rng(4).uniform(-3, 3, 2 * 19 * 3)))))
+    fused_seen = 0
+    # transports: 2 = peer memory with the swap carried by the next fused pass (default), 1 = peer memory,
+    # standalone exchange kernel, 0 = NCCL send/recv
+    for transport in (2, 1, 0):
         for name, n, gates in cases:
             sv = sharded_statevector(n, ctx)
             try:
-                sv.set_option("dist_p2p", transport)
+                sv.set_option("dist_p2p", 1 if transport else 0)
+                sv.set_option("dist_fuse_swap", 1 if transport == 2 else 0)
             except NotImplementedError:
                 if rank == 0:
                     print("P2P transport unavailable (CUDA IPC); NCCL only", flush=True)
@@ -68,10 +75,16 @@ def main():
             idx_ref = ref.tree_choice_indices_sharded(ref.tree_probabilities(full), u, world)
             mism = int(np.sum(idx != idx_ref))
             assert mism == 0, (name, mism)
+            if transport == 2:
+                fused_seen += c["fused_swaps"]
+            else:
+                assert c["fused_swaps"] == 0
             if rank == 0:
-                print(f"[{name} transport={'p2p' if transport else 'nccl'}] amp err {err:.1e} swaps {c['swap_count']} "
-                      f"passes {c['state_passes']} sample mismatches {mism}", flush=True)
+                print(f"[{name} transport={('nccl', 'p2p', 'p2p+fused')[transport]}] amp err {err:.1e} swaps "
+                      f"{c['swap_count']} (fused {c['fused_swaps']}) passes {c['state_passes']} sample mismatches {mism}",
+                      flush=True)
             del sv
+    assert fused_seen > 0, "no swap was carried by a fused pass"
     print(f"DIST_GPU_OK rank {rank} of {world}", flush=True)
 
 

@@ -150,8 +150,8 @@ def test_qft_closed_form_convention_small():
 def test_sampling_against_numpy_cumsum_at_full_width(n_req):
     """Indices vs Generator.choice's arithmetic (sequential cumsum / cdf[-1], searchsorted right):
     a parallel summation tree cannot reproduce a 2^28-term sequential chain bit for bit, so the
-    contract is: every difference is exactly one index AND the uniform is within 1e-11 of the cdf
-    boundary between the two candidates."""
+    contract is: the two answers are neighbours (a few indices apart at most) AND the uniform is within
+    1e-11 of every cdf boundary between them."""
     _lib.drain_pool()
     n = _shrink(n_req, copies_dev=2, copies_host=4)
     sv = Statevector.from_int(0, 1 << n)
@@ -167,13 +167,18 @@ def test_sampling_against_numpy_cumsum_at_full_width(n_req):
     want = np.searchsorted(cdf, u, side="right")
     diff = got - want
     bad = np.nonzero(diff)[0]
-    assert np.all(np.abs(diff[bad]) == 1), np.unique(diff)
-    lo = np.minimum(got[bad], want[bad])        # the boundary both answers straddle is cdf[lo]
-    dist = np.abs(u[bad] - cdf[lo])
-    assert bad.size == 0 or float(dist.max()) < 1e-11, float(dist.max())
-    print(f"[sampling {n}q] {bad.size} of {shots} shots differ from NumPy's cumsum by one index; "
-          f"max |u - boundary| = {float(dist.max()) if bad.size else 0.0:.2e}")
-    assert bad.size < shots * 1e-2
+    # Porter-Thomas: many outcomes have p far below the rounding noise of a 2^28-term prefix sum, so a
+    # uniform may sit within that noise of SEVERAL consecutive boundaries: the two answers may be a few
+    # indices apart, but every boundary between them must be within 1e-11 of the uniform
+    assert bad.size == 0 or int(np.max(np.abs(diff[bad]))) <= 4, np.unique(diff)
+    worst = 0.0
+    for s_ in bad:
+        lo, hi = sorted((int(got[s_]), int(want[s_])))
+        worst = max(worst, float(np.max(np.abs(u[s_] - cdf[lo:hi]))))
+    assert worst < 1e-11, worst
+    print(f"[sampling {n}q] {bad.size} of {shots} shots differ from NumPy's sequential cumsum "
+          f"(max index distance {int(np.max(np.abs(diff))) if bad.size else 0}); max |u - boundary| = {worst:.2e}")
+    assert bad.size < shots * 1e-3
 
 
 def test_collapse_and_measure_wide():
