@@ -26,11 +26,11 @@ __version__ = "0.1.0"
 
 
 def install():
-    """Opt-in: rebind Qiskit's statevector entry points to the device classes (SURVEY 8b B2 iii).
-    Only meaningful where ``import qiskit`` works; raises ImportError otherwise."""
-    import qiskit.primitives as _prims          # noqa: PLC0415 - optional dependency
-    import qiskit.quantum_info as _qi
+    """Opt-in: rebind Qiskit's statevector entry points to the device classes (SURVEY 8b B2 iii):
+    ``qiskit.quantum_info.Statevector`` -> ``DeviceStatevector(Statevector)``,
+    ``qiskit.primitives.StatevectorEstimator / StatevectorSampler`` -> ``DeviceEstimator(BaseEstimatorV2)`` /
+    ``DeviceSampler(BaseSamplerV2)`` (qiskit_b200/adapter.py).  Needs a working ``import qiskit``;
+    raises ImportError otherwise."""
+    from . import adapter                      # noqa: PLC0415 - optional dependency inside
 
-    _prims.StatevectorEstimator = StatevectorEstimator
-    _prims.StatevectorSampler = StatevectorSampler
-    _qi.Statevector = Statevector
+    return adapter.install()

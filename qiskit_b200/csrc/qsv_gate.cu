@@ -2203,20 +2203,28 @@ static bool fused_swap_capable(const qsv_state* s, const FpPass& P) {
 }
 
 static int launch_fused_swap_pass(qsv_state* s, const FpPass& P) {
-    const size_t smem = FP_TILE * sizeof(double2) + (size_t)P.ntabs * FP_NT * sizeof(uint16_t);
-    static bool attr_set = false;
-    if (!attr_set) {
-        QSV_CUDA(cudaFuncSetAttribute(k_fused_swap_pass, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      (int)(FP_TILE * sizeof(double2) + FP_MAX_TABS * FP_NT * sizeof(uint16_t))));
-        attr_set = true;
+    // two CTAs per SM: each may use half of the SM's shared memory minus the 1 KB the system reserves per CTA
+    static int smem_cta = 0;
+    if (!smem_cta) {
+        int per_sm = 0;
+        QSV_CUDA(cudaDeviceGetAttribute(&per_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, s->device));
+        int per_block = 0;
+        QSV_CUDA(cudaDeviceGetAttribute(&per_block, cudaDevAttrMaxSharedMemoryPerBlockOptin, s->device));
+        smem_cta = std::min(per_sm / 2 - 1024, per_block);
+        QSV_CUDA(cudaFuncSetAttribute(k_fused_swap_pass, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cta));
     }
+    const size_t tabs_bytes = (size_t)P.ntabs * FP_NT * sizeof(uint16_t);
     FpRemote R;
     build_fp_remote(P, *s->pending_swap, R);
+    static const int stage_max = getenv("QSV_FUSED_SWAP_STAGE") ? atoi(getenv("QSV_FUSED_SWAP_STAGE")) : 15;
+    const long spare = (long)smem_cta - (long)(FP_TILE * sizeof(double2)) - (long)tabs_bytes;
+    R.stage_rows = (int)std::max(0l, std::min<long>(std::min(stage_max, 15), spare / 4096));
+    const size_t smem = FP_TILE * sizeof(double2) + (size_t)R.stage_rows * 4096 + tabs_bytes;
     static const bool trace = getenv("QSV_TRACE") != nullptr;
     if (trace) {
         trace_fused_pass(P, stderr);
-        fprintf(stderr, "        (fused swap pass: k=%d, %d of the swapped bits are tile bits, tiles gathered over NVLink)\n",
-                R.k, R.nin);
+        fprintf(stderr, "        (fused swap pass: k=%d, %d of the swapped bits are tile bits, %d rows of the next tile staged)\n",
+                R.k, R.nin, R.stage_rows);
     }
     QSV_TRY(qsv_dist_fused_swap_begin(s, 1u << R.nin, &R.target));
     const unsigned grid = (unsigned)std::min<uint64_t>(P.ntiles, (uint64_t)s->num_sms * 2);
