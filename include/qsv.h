@@ -246,16 +246,18 @@ int qsv_flush_l2(qsv_state* s);
  * line per planned pass (kernel kind, tile bits, phases, op counts) is written to `path`. */
 int qsv_debug_plan(int n_qubits, const qsv_gate* gates, uint64_t n_gates, int flags, const char* path);
 
-/* Host-only emulation of the gather arithmetic of the fused swap pass (k_fused_swap_pass: the first
- * fused pass after a global<->local qubit swap reads its tiles from the peers' slabs): for the first
- * pass of `gates` on a slab of n_local qubits and the swap (k, lpos[], a = this rank's value on the
- * swapped global bits) every destination index x gets src_j[x] (source rank as a value of the swapped
- * global bits), src_addr[x] (local index there) and tile_of[x] (rank-relative tile number);
+/* Host-only emulation of the remote addressing of the fused swap pass (k_fused_swap_pass).  mode 1
+ * (gather): the first fused pass after a global<->local qubit swap reads its tiles from the peers' slabs;
+ * modes 2 / 3 (scatter): the last fused pass before the swap stores its tiles into the peers' slabs through
+ * its copy-out (2) or direct-store (3) mapping.  For that pass of `gates` on a slab of n_local qubits and
+ * the swap (k, lpos[], a = this rank's value on the swapped global bits) every own index x gets src_j[x]
+ * (the other rank as a value of the swapped global bits), src_addr[x] (local index there) and tile_of[x]
+ * (rank-relative tile number);
  * sig[tile * 16 + i] = ranks tile `tile` signals (0xffffffff: unused); *nin = swapped bits that are
  * tile bits; *ok = 0 when the first pass is not a fused pass.  No device work (CPU tests). */
-int qsv_debug_fused_swap(int n_local, int k, const int* lpos, int a, const qsv_gate* gates, uint64_t n_gates,
-                         uint32_t* src_j, uint64_t* src_addr, uint32_t* tile_of, uint32_t* sig, int* nin,
-                         int* ok);
+int qsv_debug_fused_swap(int mode, int n_local, int k, const int* lpos, int a, const qsv_gate* gates,
+                         uint64_t n_gates, uint32_t* src_j, uint64_t* src_addr, uint32_t* tile_of, uint32_t* sig,
+                         int* nin, int* ok);
 
 /* ---- sharded states (one process per GPU; NCCL over NVLink) -------------- */
 /* 128-byte ncclUniqueId for the bootstrap; rank 0 creates it and the host side

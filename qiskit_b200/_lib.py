@@ -102,7 +102,7 @@ PROTOTYPES = {
     "qsv_set_option": (_i, [_vp, C.c_char_p, C.c_int64]),
     "qsv_flush_l2": (_i, [_vp]),
     "qsv_debug_plan": (_i, [_i, _P(QsvGate), _u64, _i, C.c_char_p]),
-    "qsv_debug_fused_swap": (_i, [_i, _i, _P(_i), _i, _P(QsvGate), _u64, _vp, _vp, _vp, _vp, _P(_i), _P(_i)]),
+    "qsv_debug_fused_swap": (_i, [_i, _i, _i, _P(_i), _i, _P(QsvGate), _u64, _vp, _vp, _vp, _vp, _P(_i), _P(_i)]),
     "qsv_dist_unique_id": (_i, [_vp]),
     "qsv_create_dist": (_i, [_P(_vp), _i, _i, _i, _i, _vp]),
     "qsv_dist_info": (_i, [_vp, _P(_i), _P(_i), _P(_i)]),

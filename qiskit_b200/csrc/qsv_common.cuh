@@ -11,7 +11,17 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "../../include/qsv.h"
+
+// NVTX range for the enclosing scope (header-only NVTX v3: a no-op unless a profiler injects itself).
+// One range per entry point and per kernel family, so a timeline shows plan / launch / exchange phases.
+struct QsvNvtxRange {
+    explicit QsvNvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~QsvNvtxRange() { nvtxRangePop(); }
+};
+#define QSV_RANGE(name) QsvNvtxRange qsv_nvtx_range_##__LINE__(name)
 
 // ---------------------------------------------------------------- errors --
 void qsv_set_error(const char* fmt, ...);
@@ -45,6 +55,8 @@ struct qsv_dist;  // defined in qsv_dist.cu
 // the first fused pass of the next qsv_apply_hgates gathers its tiles from the peers' slabs
 // (k_fused_swap_pass); any other consumer runs the standalone exchange first (qsv_dist_flush_swap).
 struct QsvPendingSwap {
+    int mode;                 // 1: gather -- the first fused pass AFTER the swap reads its tiles from the peers
+                              // 2: scatter -- the last fused pass BEFORE the swap writes its tiles to the peers
     int k;
     int lpos[4];              // local bit paired with swapped global bit i
     int a;                    // this rank's value on the swapped global bits
@@ -134,8 +146,8 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags);
 
 // sharded states (qsv_dist.cu)
 int qsv_dist_flush_swap(qsv_state* s);                    // run a pending swap as a standalone exchange
-int qsv_dist_fused_swap_begin(qsv_state* s, uint32_t signals_per_tile, uint32_t* target_out);  // barrier + timer start
-int qsv_dist_fused_swap_end(qsv_state* s);                // timer stop, counters, handshake error check
+int qsv_dist_fused_swap_begin(qsv_state* s, uint32_t signals_per_tile, uint32_t* target_out);  // (gather: barrier) + timer start
+int qsv_dist_fused_swap_end(qsv_state* s);                // (scatter: barrier), timer stop, counters, handshake error check
 
 int qsv_materialize(qsv_state* s);  // write a pending |index> into the amplitude buffer
 int qsv_flush_product(qsv_state* s);  // write a pending product state into the amplitude buffer (qsv_gate.cu)

@@ -280,8 +280,9 @@ extern "C" int qsv_create_dist(qsv_state** out, int n_qubits, int device, int ra
         cudaStreamSynchronize(s->stream);
         d->p2p = flag > 0.5;
         d->use_p2p = d->p2p;
+        // bit 0: gather (first pass after the swap pulls), bit 1: scatter (last pass before it pushes; preferred)
         const char* fenv = getenv("QSV_DIST_FUSE_SWAP");
-        d->use_fuse = d->p2p && (fenv && *fenv ? atoi(fenv) : 1);
+        d->use_fuse = d->p2p ? (fenv && *fenv ? atoi(fenv) & 3 : 3) : 0;
     } while (0);
     if (rc != QSV_OK) {
         std::string msg = qsv_last_error();
@@ -311,7 +312,7 @@ int qsv_dist_set_option(qsv_state* s, const char* name, int64_t value) {
     }
     if (!strcmp(name, "dist_fuse_swap")) {
         if (value && !s->dist->p2p) QSV_FAIL(QSV_ERR_UNSUPPORTED, "peer slabs are not mapped (CUDA IPC unavailable)");
-        s->dist->use_fuse = value != 0;
+        s->dist->use_fuse = (int)(value & 3);  // 0 off, 1 gather, 2 scatter, 3 both (scatter where it applies)
         return QSV_OK;
     }
     if (!strcmp(name, "dist_min_lpos")) {
@@ -437,6 +438,7 @@ static void swap_commit_perm(qsv_state* s, int k, const int* gpos, const int* lp
 
 // the standalone exchange (data movement only; perm is the caller's business)
 static int swap_execute(qsv_state* s, int k, const int* gpos, const int* lpos) {
+    QSV_RANGE("qsv:qubit_swap");
     qsv_dist* d = s->dist;
     SwapArgs A;
     int peers_rank[1 << MAX_G];
@@ -516,13 +518,14 @@ static int dist_swap_bits(qsv_state* s, int k, const int* gpos, const int* lpos)
 
 // ---- fused swap pass plumbing (the kernel and its descriptors live in qsv_fused.cuh / qsv_gate.cu) ----
 // Plan the swap, update perm, and leave the data movement to the first fused pass that follows.
-static int swap_defer(qsv_state* s, int k, const int* gpos, const int* lpos) {
+static int swap_defer(qsv_state* s, int k, const int* gpos, const int* lpos, int mode) {
     qsv_dist* d = s->dist;
     SwapArgs A;
     int peers_rank[1 << MAX_G];
     QSV_TRY(swap_args(s, k, gpos, lpos, A, peers_rank));
     QsvPendingSwap& W = d->pending;
     memset(&W, 0, sizeof W);
+    W.mode = mode;
     W.k = k;
     W.a = A.a;
     for (int i = 0; i < k; ++i) {
@@ -535,7 +538,7 @@ static int swap_defer(qsv_state* s, int k, const int* gpos, const int* lpos) {
         W.flag[j] = d->peer_flags[peers_rank[j]];
     }
     W.err = d->flags + (d->flag_words - 1);
-    swap_commit_perm(s, k, gpos, lpos);
+    if (mode == 1) swap_commit_perm(s, k, gpos, lpos);  // gather: the run that follows already sees the new layout
     s->pending_swap = &W;
     return QSV_OK;
 }
@@ -558,12 +561,18 @@ int qsv_dist_fused_swap_begin(qsv_state* s, uint32_t signals_per_tile, uint32_t*
     QSV_CUDA(cudaEventCreate(&e0));
     QSV_CUDA(cudaEventRecord(e0, s->stream));
     d->fused_e0 = e0;
-    // every rank's earlier work on its slab must be complete before anybody gathers from it
-    return dist_barrier(s);
+    // gather: every rank's earlier work on its slab must be complete before anybody reads from it.
+    // (scatter needs nothing here: nobody writes into a region before its owner has signalled that it
+    // has loaded it, and the owner's own earlier work precedes its loads in stream order.)
+    if (d->pending.mode == 1) return dist_barrier(s);
+    return QSV_OK;
 }
 
 int qsv_dist_fused_swap_end(qsv_state* s) {
     qsv_dist* d = s->dist;
+    // scatter: a rank's kernel ends when IT has stored everything, its peers may still be writing into
+    // its slab: nobody touches its slab again before everybody's scatter pass has completed
+    if (d->pending.mode == 2) QSV_TRY(dist_barrier(s));
     cudaEvent_t e1 = nullptr;
     QSV_CUDA(cudaEventCreate(&e1));
     QSV_CUDA(cudaEventRecord(e1, s->stream));
@@ -583,8 +592,8 @@ int qsv_dist_fused_swap_end(qsv_state* s) {
         float ms = 0.f;
         cudaEventElapsedTime(&ms, d->fused_e0, e1);
         const double gb = (double)npeers * (16ull << (s->n_local - k)) / 1e9;
-        fprintf(stderr, "[fused swap pass] k=%d gathered %.2f GB/rank in %.3f ms = %.1f GB/s per direction\n", k, gb, ms,
-                gb / (ms / 1e3));
+        fprintf(stderr, "[fused swap pass] k=%d %s %.2f GB/rank in %.3f ms = %.1f GB/s per direction\n", k,
+                d->pending.mode == 1 ? "gathered" : "scattered", gb, ms, gb / (ms / 1e3));
     }
     if (*h) QSV_FAIL(QSV_ERR_NCCL, "fused swap pass: a peer did not arrive in time (handshake timeout)");
     return QSV_OK;
@@ -738,6 +747,7 @@ static int dist_do_swap(qsv_state* s, const PlanStep& st) {
 
 // gates carry LOGICAL qubits in q[]
 int qsv_dist_apply(qsv_state* s, std::vector<HGate>& gates, int flags) {
+    QSV_RANGE("qsv:dist_plan_and_apply");
     qsv_dist* d = s->dist;
     if (!d) QSV_FAIL(QSV_ERR_INVALID, "state is not sharded");
     std::vector<PlanGate> pg(gates.size());
@@ -749,14 +759,16 @@ int qsv_dist_apply(qsv_state* s, std::vector<HGate>& gates, int flags) {
     std::vector<PlanStep> steps;
     QSV_TRY(dist_plan(s->n, s->n_local, s->perm, pg, d->min_lpos, steps));
     cplx scalar(1.0, 0.0);
+    const bool may_fuse = d->use_p2p && !(flags & QSV_FLAG_NO_FUSION) && s->n_local >= 12;
+    std::vector<char> swap_done(steps.size(), 0);
     for (size_t si = 0; si < steps.size(); ++si) {
         const PlanStep& st = steps[si];
         if (st.kind == 1) {
-            // Fused swap pass: when every gate of the following run is fully local after the swap, all
-            // ranks hold the same gate list, plan the same passes, and the first fused pass can gather its
+            if (swap_done[si]) continue;  // rode inside the last pass of the previous run (scatter)
+            // Fused swap pass, gather: when every gate of the following run is fully local after the swap,
+            // all ranks hold the same gate list, plan the same passes, and the first fused pass can read its
             // tiles from the peers (qsv_gate.cu takes it from there, or falls back to the standalone kernel)
-            bool defer = d->use_fuse && d->use_p2p && !(flags & QSV_FLAG_NO_FUSION) && si + 1 < steps.size() &&
-                         steps[si + 1].kind == 0 && s->n_local >= 12;
+            bool defer = may_fuse && (d->use_fuse & 1) && si + 1 < steps.size() && steps[si + 1].kind == 0;
             if (defer) {
                 int perm2[64];
                 memcpy(perm2, s->perm, sizeof perm2);
@@ -770,7 +782,7 @@ int qsv_dist_apply(qsv_state* s, std::vector<HGate>& gates, int flags) {
                     gpos[i] = s->perm[st.gin[i]];
                     lpos[i] = s->perm[st.lout[i]];
                 }
-                QSV_TRY(swap_defer(s, st.k, gpos, lpos));
+                QSV_TRY(swap_defer(s, st.k, gpos, lpos, 1));
             } else {
                 QSV_TRY(dist_do_swap(s, st));
             }
@@ -778,6 +790,7 @@ int qsv_dist_apply(qsv_state* s, std::vector<HGate>& gates, int flags) {
         }
         std::vector<HGate> local;
         local.reserve(st.gates.size());
+        bool all_local = true;
         for (int id : st.gates) {
             const HGate& g = gates[id];
             int phys[QSV_MAX_GATE_QUBITS];
@@ -792,6 +805,7 @@ int qsv_dist_apply(qsv_state* s, std::vector<HGate>& gates, int flags) {
                 local.push_back(std::move(h));
                 continue;
             }
+            all_local = false;
             HGate h;
             cplx sc;
             bool is_scalar;
@@ -811,6 +825,20 @@ int qsv_dist_apply(qsv_state* s, std::vector<HGate>& gates, int flags) {
             }
             if (!ident) local.push_back(std::move(h));
         }
+        // Fused swap pass, scatter (preferred: remote writes are posted, remote reads are not): the swap
+        // that FOLLOWS this run rides inside the run's last fused pass, which stores its tiles straight
+        // into the slabs that own them after the swap.  Same condition: all ranks plan the same passes.
+        const bool scatter = may_fuse && (d->use_fuse & 2) && all_local && !local.empty() && !s->pending_swap &&
+                             si + 1 < steps.size() && steps[si + 1].kind == 1;
+        if (scatter) {
+            const PlanStep& sw = steps[si + 1];
+            int gpos[MAX_G], lpos[MAX_G];
+            for (int i = 0; i < sw.k; ++i) {
+                gpos[i] = s->perm[sw.gin[i]];
+                lpos[i] = s->perm[sw.lout[i]];
+            }
+            QSV_TRY(swap_defer(s, sw.k, gpos, lpos, 2));
+        }
         // a rank-dependent scalar must not change what the planner sees while a swap is pending
         // (every rank has to cut the same passes): it waits for the next run or the final qsv_scale
         if (scalar != cplx(1.0, 0.0) && !local.empty() && !s->pending_swap) {
@@ -819,6 +847,16 @@ int qsv_dist_apply(qsv_state* s, std::vector<HGate>& gates, int flags) {
         }
         if (!local.empty()) QSV_TRY(qsv_apply_hgates(s, local, flags));
         else if (s->pending_swap) QSV_TRY(qsv_dist_flush_swap(s));
+        if (scatter) {
+            const PlanStep& sw = steps[si + 1];
+            if (s->pending_swap) {  // the last pass could not carry it: standalone exchange
+                s->pending_swap = nullptr;
+                QSV_TRY(dist_do_swap(s, sw));
+            } else {
+                swap_commit_perm(s, d->pending_k, d->pending_gpos, d->pending.lpos);
+            }
+            swap_done[si + 1] = 1;
+        }
     }
     if (s->pending_swap) QSV_TRY(qsv_dist_flush_swap(s));
     if (scalar != cplx(1.0, 0.0)) QSV_TRY(qsv_scale(s, scalar.real(), scalar.imag()));

@@ -364,6 +364,7 @@ struct QwcGroup {
 
 extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, const uint64_t* z_masks,
                                       const uint64_t* x_masks, const double* phases, double* out) {
+    QSV_RANGE("qsv_expval_pauli_batch");
     qsv_state* s = const_cast<qsv_state*>(cs);
     if (!s || (n_terms && (!z_masks || !x_masks || !out)))
         QSV_FAIL(QSV_ERR_INVALID, "qsv_expval_pauli_batch: NULL argument");

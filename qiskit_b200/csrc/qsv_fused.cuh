@@ -144,6 +144,14 @@ struct FpRemote {
     // per CTA in flight during the phases; they are moved into the tile buffer (each thread moves the
     // elements it loaded itself) once the current tile has left it.
     int32_t stage_rows;
+    // ---- scatter mode (k_fused_swap_pass<2>): the LAST fused pass before the swap reads its own slab and
+    // stores every tile into the slabs of the ranks that own it after the swap.  Remote WRITES are posted
+    // (measured: a B200 sustains ~340 GB/s of remote reads but about twice that of remote writes), and the
+    // same handshake orders them: a rank signals that it has loaded tile i before anybody may overwrite it.
+    // Direct-store phase: register r of thread t goes to rank j = j_tile | j_thread | st_jreg[r].
+    int8_t st_thr_bit[FPR_MAXK];         // [i]: direct-store thread bit (0..7) carrying swapped local bit i, or -1
+    uint8_t st_jreg[16];                 // bits of j contributed by register r
+    uint64_t st_clean[16];               // P.st_off[r] with the swapped bits cleared
 };
 
 __host__ __device__ __forceinline__ uint64_t fp_tile_base(const FpPass& P, uint32_t tile) {
@@ -164,6 +172,19 @@ __host__ __device__ __forceinline__ uint32_t fpr_j_thread(const FpRemote& R, uin
     for (int i = 0; i < R.k; ++i)
         if (R.thr_bit[i] >= 0) j |= ((t >> R.thr_bit[i]) & 1u) << i;
     return j;
+}
+// bits of j carried by direct-store thread t (scatter mode)
+__host__ __device__ __forceinline__ uint32_t fpr_j_store_thread(const FpRemote& R, uint32_t t) {
+    uint32_t j = 0;
+    for (int i = 0; i < R.k; ++i)
+        if (R.st_thr_bit[i] >= 0) j |= ((t >> R.st_thr_bit[i]) & 1u) << i;
+    return j;
+}
+// direct-store thread offset (elements) of thread t
+__host__ __device__ __forceinline__ uint64_t fp_st_thread(const FpPass& P, uint32_t t) {
+    uint64_t o = 0;
+    for (int b = 0; b < 8; ++b) o |= (uint64_t)((t >> b) & 1u) << P.pos[P.st_tpos[b]];
+    return o;
 }
 // copy-in thread offset (elements) of thread t: tile bits 0..7 scattered to their index positions
 __host__ __device__ __forceinline__ uint64_t fp_cp_off(const FpPass& P, uint32_t t) {
@@ -417,11 +438,14 @@ __device__ __forceinline__ void fpr_wait(const FpRemote& R, uint32_t tile) {
 // copies are issued before that phase's arithmetic.
 // `src` = `amp` for the usual in-place pass; a different `src` makes the pass out of place (tiles are
 // read from src and written to amp), which saves the scratch copy of basis-change expectation values.
-template <bool REMOTE>
+// MODE 0: plain pass.  MODE 1: fused swap pass, gather (tiles read from the peers' slabs, see FpRemote).
+// MODE 2: fused swap pass, scatter (tiles stored into the peers' slabs).
+template <int MODE>
 __device__ __forceinline__ void fp_pass_body(double2* amp, const double2* src, const FpPass& P, const FpRemote& R) {
+    constexpr bool REMOTE = MODE != 0, GATHER = MODE == 1, SCATTER = MODE == 2;
     extern __shared__ __align__(16) unsigned char fp_smem[];
     unsigned char* const tilebuf = fp_smem;
-    const int stage_rows = REMOTE ? R.stage_rows : 0;
+    const int stage_rows = GATHER ? R.stage_rows : 0;
     unsigned char* const stagebuf = fp_smem + FP_TILE * sizeof(double2);  // REMOTE only: [stage_rows][4 KB]
     uint16_t* const tabs_sm = reinterpret_cast<uint16_t*>(fp_smem + FP_TILE * sizeof(double2) + (size_t)stage_rows * 4096);
     const uint32_t t = threadIdx.x;
@@ -441,6 +465,8 @@ __device__ __forceinline__ void fp_pass_body(double2* amp, const double2* src, c
     // fused swap pass: this thread's share of the source-rank selector and its cleaned offset
     const uint32_t rj_thr = REMOTE ? fpr_j_thread(R, t) : 0u;
     const uint64_t rcp_clean = REMOTE ? (cp_off & ~R.lmask) : 0ull;
+    const uint32_t sj_thr = SCATTER ? fpr_j_store_thread(R, t) : 0u;
+    const uint64_t sst_clean = SCATTER ? (st_thread & ~R.lmask) : 0ull;
 
     auto tile_base_of = [&](uint32_t tile) {
         const uint64_t base = fp_tile_base(P, tile);
@@ -474,10 +500,10 @@ __device__ __forceinline__ void fp_pass_body(double2* amp, const double2* src, c
     };
     auto issue_load = [&](uint64_t tile_base) {
         const uint32_t dst0 = (uint32_t)__cvta_generic_to_shared(tilebuf);
-        if (REMOTE) {
+        if (GATHER) {
             issue_remote_rows(tile_base, 0, 16, tilebuf);
             return;
-        } else if (P.gen_h > 0) {
+        } else if (!REMOTE && P.gen_h > 0) {
             const char* g = reinterpret_cast<const char*>(P.gen_tile + t);
 #pragma unroll
             for (int r = 0; r < 16; ++r) {
@@ -510,7 +536,7 @@ __device__ __forceinline__ void fp_pass_body(double2* amp, const double2* src, c
         const uint32_t next = tile + gridDim.x;
         const bool has_next = next < P.ntiles;
         const uint64_t next_base = has_next ? tile_base_of(next) : 0;
-        if (REMOTE && has_next && stage_rows > 0) issue_remote_rows(next_base, 0, stage_rows, stagebuf);
+        if (GATHER && has_next && stage_rows > 0) issue_remote_rows(next_base, 0, stage_rows, stagebuf);
         const uint64_t diag_base = tile_base | P.index_base;
         if (!REMOTE && P.gen_h > 0 && has_next) {  // the next tile's two table entries: into L1 ahead of their use
             asm volatile("prefetch.global.L1 [%0];\n" ::"l"(P.gen_lo + (next_base & ((1ull << P.gen_h) - 1))));
@@ -537,7 +563,7 @@ __device__ __forceinline__ void fp_pass_body(double2* amp, const double2* src, c
                 if (REMOTE && t == 0) fpr_wait(R, tile);  // ... and the peers have read what this tile overwrites
                 __syncthreads();
                 if (has_next) {
-                    if (REMOTE) finish_remote_load(next_base);
+                    if (GATHER) finish_remote_load(next_base);
                     else issue_load(next_base);
                 }
             }
@@ -562,6 +588,13 @@ __device__ __forceinline__ void fp_pass_body(double2* amp, const double2* src, c
                     for (int r = 0; r < 16; ++r)
                         *reinterpret_cast<double*>(g + P.st_off[r] - (((P.st_off[r] >> 4) & 15ull) << 3)) =
                             v[r].x * v[r].x + v[r].y * v[r].y;
+                } else if (SCATTER) {
+                    const uint32_t jt = fpr_j_tile(R, tile_base) | sj_thr;
+                    const uint64_t off = ((tile_base & ~R.lmask) | R.a_l) + sst_clean;
+#pragma unroll
+                    for (int r = 0; r < 16; ++r)
+                        *reinterpret_cast<double2*>(reinterpret_cast<char*>(const_cast<double2*>(R.peer[jt | R.st_jreg[r]]) + off) +
+                                                    R.st_clean[r]) = v[r];
                 } else {
 #pragma unroll
                     for (int r = 0; r < 16; ++r) *reinterpret_cast<double2*>(g + P.st_off[r]) = v[r];
@@ -580,14 +613,24 @@ __device__ __forceinline__ void fp_pass_body(double2* amp, const double2* src, c
                 __syncthreads();
             }
             const uint32_t so16 = P.out_tab == 0xffff ? st16 : ((uint32_t)tabs_sm[P.out_tab * FP_NT + t] << 4);
-            char* g = reinterpret_cast<char*>(amp + tile_base + cp_off);
+            if (SCATTER) {
+                const uint32_t jt = fpr_j_tile(R, tile_base) | rj_thr;
+                const uint64_t off = ((tile_base & ~R.lmask) | R.a_l) + rcp_clean;
 #pragma unroll
-            for (int r = 0; r < 16; ++r)
-                *reinterpret_cast<double2*>(g + P.row_off[r]) =
-                    *reinterpret_cast<const double2*>(tilebuf + (so16 ^ P.out_row[r]));
+                for (int r = 0; r < 16; ++r)
+                    *reinterpret_cast<double2*>(reinterpret_cast<char*>(const_cast<double2*>(R.peer[jt | R.jrow[r]]) + off) +
+                                                R.row_clean[r]) =
+                        *reinterpret_cast<const double2*>(tilebuf + (so16 ^ P.out_row[r]));
+            } else {
+                char* g = reinterpret_cast<char*>(amp + tile_base + cp_off);
+#pragma unroll
+                for (int r = 0; r < 16; ++r)
+                    *reinterpret_cast<double2*>(g + P.row_off[r]) =
+                        *reinterpret_cast<const double2*>(tilebuf + (so16 ^ P.out_row[r]));
+            }
             __syncthreads();
             if (has_next) {
-                if (REMOTE) finish_remote_load(next_base);
+                if (GATHER) finish_remote_load(next_base);
                 else issue_load(next_base);
             }
         }
@@ -598,13 +641,15 @@ __device__ __forceinline__ void fp_pass_body(double2* amp, const double2* src, c
 }
 
 __global__ void __launch_bounds__(FP_NT, 2) k_fused_pass(double2* amp, const double2* src, const __grid_constant__ FpPass P) {
-    fp_pass_body<false>(amp, src, P, *reinterpret_cast<const FpRemote*>(&P));  // R is never read
+    fp_pass_body<0>(amp, src, P, *reinterpret_cast<const FpRemote*>(&P));  // R is never read
 }
 
-// the same pass with its tiles gathered from the peers' slabs (see FpRemote)
+// the same pass carrying a global<->local qubit swap: MODE 1 gathers its tiles from the peers' slabs
+// (first pass after the swap), MODE 2 scatters them into the peers' slabs (last pass before it)
+template <int MODE>
 __global__ void __launch_bounds__(FP_NT, 2) k_fused_swap_pass(double2* amp, const __grid_constant__ FpPass P,
                                                               const __grid_constant__ FpRemote R) {
-    fp_pass_body<true>(amp, amp, P, R);
+    fp_pass_body<MODE>(amp, amp, P, R);
 }
 
 // ---- k_fused_pass3: the same pass with THREE tile buffers per SM --------------------------------

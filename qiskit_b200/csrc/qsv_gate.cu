@@ -960,6 +960,7 @@ static int launch_tile_pass(qsv_state* s, const PassParams& P, uint64_t ntiles) 
 }
 
 static int apply_dense_big(qsv_state* s, const HGate& g) {
+    QSV_RANGE("qsv:dense_big");
     const int k = g.k;
     const size_t dim = (size_t)1 << k;
     // scratch layout: [matrix dim*dim double2][qsorted k ints][qbits k ints]
@@ -2193,6 +2194,20 @@ static void build_fp_remote(const FpPass& P, const QsvPendingSwap& W, FpRemote& 
         R.jrow[r] = (uint8_t)jr;
         R.row_clean[r] = clean * sizeof(double2);
     }
+    // scatter mode, direct-store phase: the same decomposition for the store mapping
+    for (int i = 0; i < W.k; ++i) {
+        R.st_thr_bit[i] = -1;
+        for (int j = 0; j < 8; ++j)
+            if (P.pos[P.st_tpos[j]] == W.lpos[i]) R.st_thr_bit[i] = (int8_t)j;
+    }
+    for (int r = 0; r < 16; ++r) {
+        uint32_t jr = 0;
+        const uint64_t off = P.st_off[r] / sizeof(double2);
+        for (int i = 0; i < W.k; ++i)
+            if ((off >> W.lpos[i]) & 1ull) jr |= 1u << i;
+        R.st_jreg[r] = (uint8_t)jr;
+        R.st_clean[r] = (off & ~R.lmask) * sizeof(double2);
+    }
     static const long long to_ms = getenv("QSV_FUSED_SWAP_TIMEOUT_MS") ? atoll(getenv("QSV_FUSED_SWAP_TIMEOUT_MS")) : 4000;
     R.timeout = to_ms * 2000000ll;  // ~2 GHz SM clock
 }
@@ -2203,6 +2218,8 @@ static bool fused_swap_capable(const qsv_state* s, const FpPass& P) {
 }
 
 static int launch_fused_swap_pass(qsv_state* s, const FpPass& P) {
+    const int mode = s->pending_swap->mode;
+    QSV_RANGE("qsv:fused_swap_pass");
     // two CTAs per SM: each may use half of the SM's shared memory minus the 1 KB the system reserves per CTA
     static int smem_cta = 0;
     if (!smem_cta) {
@@ -2211,24 +2228,26 @@ static int launch_fused_swap_pass(qsv_state* s, const FpPass& P) {
         int per_block = 0;
         QSV_CUDA(cudaDeviceGetAttribute(&per_block, cudaDevAttrMaxSharedMemoryPerBlockOptin, s->device));
         smem_cta = std::min(per_sm / 2 - 1024, per_block);
-        QSV_CUDA(cudaFuncSetAttribute(k_fused_swap_pass, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cta));
+        QSV_CUDA(cudaFuncSetAttribute(k_fused_swap_pass<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cta));
+        QSV_CUDA(cudaFuncSetAttribute(k_fused_swap_pass<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_cta));
     }
     const size_t tabs_bytes = (size_t)P.ntabs * FP_NT * sizeof(uint16_t);
     FpRemote R;
     build_fp_remote(P, *s->pending_swap, R);
     static const int stage_max = getenv("QSV_FUSED_SWAP_STAGE") ? atoi(getenv("QSV_FUSED_SWAP_STAGE")) : 15;
     const long spare = (long)smem_cta - (long)(FP_TILE * sizeof(double2)) - (long)tabs_bytes;
-    R.stage_rows = (int)std::max(0l, std::min<long>(std::min(stage_max, 15), spare / 4096));
+    R.stage_rows = mode == 1 ? (int)std::max(0l, std::min<long>(std::min(stage_max, 15), spare / 4096)) : 0;
     const size_t smem = FP_TILE * sizeof(double2) + (size_t)R.stage_rows * 4096 + tabs_bytes;
     static const bool trace = getenv("QSV_TRACE") != nullptr;
     if (trace) {
         trace_fused_pass(P, stderr);
-        fprintf(stderr, "        (fused swap pass: k=%d, %d of the swapped bits are tile bits, %d rows of the next tile staged)\n",
-                R.k, R.nin, R.stage_rows);
+        fprintf(stderr, "        (fused swap pass, %s: k=%d, %d of the swapped bits are tile bits, %d rows of the next tile staged)\n",
+                mode == 1 ? "gather" : "scatter", R.k, R.nin, R.stage_rows);
     }
     QSV_TRY(qsv_dist_fused_swap_begin(s, 1u << R.nin, &R.target));
     const unsigned grid = (unsigned)std::min<uint64_t>(P.ntiles, (uint64_t)s->num_sms * 2);
-    k_fused_swap_pass<<<grid, FP_NT, smem, s->stream>>>(s->amp, P, R);
+    if (mode == 1) k_fused_swap_pass<1><<<grid, FP_NT, smem, s->stream>>>(s->amp, P, R);
+    else k_fused_swap_pass<2><<<grid, FP_NT, smem, s->stream>>>(s->amp, P, R);
     QSV_CUDA(cudaGetLastError());
     s->pending_swap = nullptr;
     s->ctr.kernel_launches++;
@@ -2236,12 +2255,16 @@ static int launch_fused_swap_pass(qsv_state* s, const FpPass& P) {
     return qsv_dist_fused_swap_end(s);
 }
 
-static int launch_fused_pass(qsv_state* s, const FusedBuilt& fb) {
+static int launch_fused_pass(qsv_state* s, const FusedBuilt& fb, bool is_last) {
+    QSV_RANGE("qsv:fused_pass");
     const FpPass& P = fb.P;
-    if (s->pending_swap) {
+    if (s->pending_swap && s->pending_swap->mode == 1) {  // gather: the first pass after the swap, or nobody
         if (fused_swap_capable(s, P)) return launch_fused_swap_pass(s, P);
         QSV_TRY(qsv_dist_flush_swap(s));
     }
+    // scatter: only the last pass of the run may carry it (the caller runs the standalone exchange otherwise)
+    if (s->pending_swap && s->pending_swap->mode == 2 && is_last && fused_swap_capable(s, P))
+        return launch_fused_swap_pass(s, P);
     const size_t smem = FP_TILE * sizeof(double2) + (size_t)P.ntabs * FP_NT * sizeof(uint16_t);
     static bool attr_set = false;
     if (!attr_set) {
@@ -2326,6 +2349,7 @@ static bool direct_capable(const HGate& g) {
 }
 
 static int launch_direct(qsv_state* s, const HGate& g) {
+    QSV_RANGE("qsv:direct_gate");
     const bool real = mat_is_real(g.m);
     const uint64_t groups = qsv_local_size(s) >> g.k;
     uint64_t blocks = (groups + 255) / 256;
@@ -2359,10 +2383,12 @@ static bool tile_capable(const HGate& g) {
 
 // Apply classified gates whose qubits are all local (physical bits < n_local).
 static thread_local FILE* g_plan_dump = nullptr;
-static thread_local FpPass* g_capture_first = nullptr;   // qsv_debug_fused_swap: copy of the first fused pass
-static thread_local int g_capture_state = 0;             // 0 nothing seen, 1 captured, 2 first pass is not a fused pass
+static thread_local FpPass* g_capture_first = nullptr;   // qsv_debug_fused_swap: copy of the first (gather) / last (scatter) fused pass
+static thread_local int g_capture_state = 0;             // 0 nothing seen, 1 captured, 2 that pass is not a fused pass
+static thread_local int g_capture_last = 0;              // capture the last pass of the stream instead of the first
 
 int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
+    QSV_RANGE("qsv:plan_and_apply");
     const bool no_fusion = flags & QSV_FLAG_NO_FUSION;
     const bool want_prob = s->prob_store_req != 0;  // one-shot request (qsv_expval.cu)
     s->prob_store_req = 0;
@@ -2409,9 +2435,10 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
                 }
             }
             if (g_plan_dump) {  // host-only planning (qsv_debug_plan): report and skip the device work
-                if (g_capture_first && g_capture_state == 0 && !passes.empty()) {
-                    if (kind[0] == 3) {
-                        *g_capture_first = fparams[0].P;
+                if (g_capture_first && !passes.empty() && (g_capture_last || g_capture_state == 0)) {
+                    const size_t which = g_capture_last ? passes.size() - 1 : 0;
+                    if (kind[which] == 3 && (!g_capture_last || end == gates.size())) {
+                        *g_capture_first = fparams[which].P;
                         g_capture_state = 1;
                     } else {
                         g_capture_state = 2;
@@ -2440,7 +2467,8 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
                 s->ctr.h2d_bytes += used;
             }
             if (!passes.empty() && kind[0] != 3) QSV_TRY(qsv_flush_product(s));
-            if (s->pending_swap && (passes.empty() || kind[0] != 3)) QSV_TRY(qsv_dist_flush_swap(s));
+            if (s->pending_swap && s->pending_swap->mode == 1 && (passes.empty() || kind[0] != 3))
+                QSV_TRY(qsv_dist_flush_swap(s));
             if (s->read_from && kind[0] != 3) {  // out-of-place request, but the first pass cannot do it
                 QSV_CUDA(cudaMemcpyAsync(s->amp, s->read_from, (size_t)16 << s->n_local, cudaMemcpyDeviceToDevice,
                                          s->stream));
@@ -2461,7 +2489,7 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
                 } else if (kind[i] == 3) {
                     fparams[i].P.tabs = (const uint16_t*)(base + fparams[i].tabs_off);
                     fparams[i].P.gdata = (const double2*)(base + fparams[i].gdata_off);
-                    QSV_TRY(launch_fused_pass(s, fparams[i]));
+                    QSV_TRY(launch_fused_pass(s, fparams[i], end == gates.size() && i + 1 == passes.size()));
                 } else if (kind[i] == 1) {
                     cparams[i].phases = (const ClPhase*)(base + ops_off[i]);
                     cparams[i].subs = (const ClSub*)(base + subs_off[i]);
@@ -2476,7 +2504,7 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
         }
         if (end < gates.size()) {
             QSV_TRY(qsv_flush_product(s));
-            if (s->pending_swap) QSV_TRY(qsv_dist_flush_swap(s));
+            if (s->pending_swap && s->pending_swap->mode == 1) QSV_TRY(qsv_dist_flush_swap(s));
             if (s->read_from) {
                 QSV_CUDA(cudaMemcpyAsync(s->amp, s->read_from, (size_t)16 << s->n_local, cudaMemcpyDeviceToDevice,
                                          s->stream));
@@ -2488,7 +2516,7 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
         }
         start = end;
     }
-    if (s->pending_swap) QSV_TRY(qsv_dist_flush_swap(s));  // nothing consumed it (empty stream)
+    if (s->pending_swap && s->pending_swap->mode == 1) QSV_TRY(qsv_dist_flush_swap(s));  // nothing consumed it (empty stream)
     return QSV_OK;
 }
 
@@ -2635,6 +2663,7 @@ int qsv_flush_product(qsv_state* s) {
 }
 
 extern "C" int qsv_apply_gates(qsv_state* s, const qsv_gate* gates, uint64_t n_gates, int flags) {
+    QSV_RANGE("qsv_apply_gates");
     if (!s || (!gates && n_gates)) QSV_FAIL(QSV_ERR_INVALID, "qsv_apply_gates: NULL argument");
     QSV_CUDA(cudaSetDevice(s->device));
     return qsv_apply_gates_impl(s, gates, n_gates, flags);
@@ -2751,9 +2780,10 @@ extern "C" int qsv_apply_diagonal(qsv_state* s, const double* diag, int k, const
 // RELATIVE tile number that owns x; sig[tile * 16 + i] lists the ranks (as j values) tile `tile`
 // signals (0xffffffff = unused).  Uses the same FpPass / FpRemote builders and the same
 // __host__ __device__ helpers as the kernel.  *ok = 0 when the first pass is not a fused pass.
-extern "C" int qsv_debug_fused_swap(int n_local, int k, const int* lpos, int a, const qsv_gate* gates, uint64_t n_gates,
-                                    uint32_t* src_j, uint64_t* src_addr, uint32_t* tile_of, uint32_t* sig,
-                                    int* nin_out, int* ok) {
+extern "C" int qsv_debug_fused_swap(int mode, int n_local, int k, const int* lpos, int a, const qsv_gate* gates,
+                                    uint64_t n_gates, uint32_t* src_j, uint64_t* src_addr, uint32_t* tile_of,
+                                    uint32_t* sig, int* nin_out, int* ok) {
+    if (mode < 1 || mode > 3) QSV_FAIL(QSV_ERR_INVALID, "qsv_debug_fused_swap: mode must be 1 (gather), 2 (scatter, copy-out) or 3 (scatter, direct store)");
     if (n_local < FP_T || n_local > 30 || k < 1 || k > FPR_MAXK || !lpos || !src_j || !src_addr || !tile_of || !sig || !ok)
         QSV_FAIL(QSV_ERR_INVALID, "qsv_debug_fused_swap: bad argument");
     qsv_state st;
@@ -2769,13 +2799,16 @@ extern "C" int qsv_debug_fused_swap(int n_local, int k, const int* lpos, int a, 
     g_plan_dump = f;
     g_capture_first = P;
     g_capture_state = 0;
+    g_capture_last = mode != 1;
     cudaSetDevice(0);
     cudaGetLastError();
     int rc = qsv_apply_gates_impl(&st, gates, n_gates, 0);
     g_plan_dump = nullptr;
     g_capture_first = nullptr;
     fclose(f);
+    g_capture_last = 0;
     *ok = (rc == QSV_OK && g_capture_state == 1) ? 1 : 0;
+    if (*ok && mode == 3 && !(P->nphases > 0 && P->phases[P->nphases - 1].direct)) *ok = 0;  // no direct-store phase
     if (!*ok) {
         delete P;
         return rc;
@@ -2794,7 +2827,22 @@ extern "C" int qsv_debug_fused_swap(int n_local, int k, const int* lpos, int a, 
         const uint64_t base = fp_tile_base(*P, tile) ^ R.out_xor;
         const uint32_t jt = fpr_j_tile(R, base);
         for (uint32_t x = 0; x < 16; ++x) sig[(size_t)tile * 16 + x] = x < (1u << R.nin) ? fpr_signal_peer(R, jt, x) : 0xffffffffu;
-        for (uint32_t t = 0; t < FP_NT; ++t) {
+        for (uint32_t t = 0; t < FP_NT && mode == 3; ++t) {   // scatter through the direct-store mapping
+            const uint64_t stt = fp_st_thread(*P, t);
+            const uint32_t jth = fpr_j_store_thread(R, t);
+            for (int r = 0; r < 16; ++r) {
+                const uint64_t own = base + stt + P->st_off[r] / sizeof(double2);
+                if (own >= count || tile_of[own] != 0xffffffffu) {
+                    delete P;
+                    QSV_FAIL(QSV_ERR_INVALID, "qsv_debug_fused_swap: element %llu covered twice or out of range",
+                             (unsigned long long)own);
+                }
+                tile_of[own] = tile;
+                src_j[own] = jt | jth | R.st_jreg[r];
+                src_addr[own] = ((base & ~R.lmask) | R.a_l) + (stt & ~R.lmask) + R.st_clean[r] / sizeof(double2);
+            }
+        }
+        for (uint32_t t = 0; t < FP_NT && mode != 3; ++t) {   // copy-in (gather) / copy-out (scatter) mapping
             const uint64_t cp = fp_cp_off(*P, t);
             const uint32_t jth = fpr_j_thread(R, t);
             for (int r = 0; r < 16; ++r) {

@@ -386,6 +386,7 @@ static int marginal_to_device(qsv_state* s, const GatherBits& G, double* d_out) 
 }
 
 extern "C" int qsv_probabilities(const qsv_state* cs, const int* qargs, int m, double* host_out) {
+    QSV_RANGE("qsv_probabilities");
     qsv_state* s = const_cast<qsv_state*>(cs);
     if (!s || !host_out) QSV_FAIL(QSV_ERR_INVALID, "qsv_probabilities: NULL argument");
     if (!qargs) m = s->n;
@@ -416,6 +417,7 @@ extern "C" int qsv_probabilities(const qsv_state* cs, const int* qargs, int m, d
 
 extern "C" int qsv_sample(const qsv_state* cs, const int* qargs, int m, const double* uniforms,
                           uint64_t shots, uint64_t* out_indices, double* total_out) {
+    QSV_RANGE("qsv_sample");
     qsv_state* s = const_cast<qsv_state*>(cs);
     if (!s || (shots && (!uniforms || !out_indices))) QSV_FAIL(QSV_ERR_INVALID, "qsv_sample: NULL argument");
     if (!qargs) m = s->n;
@@ -539,6 +541,7 @@ extern "C" int qsv_sample(const qsv_state* cs, const int* qargs, int m, const do
 
 extern "C" int qsv_collapse(qsv_state* s, const int* qargs, int m, uint64_t outcome, double scale,
                             int rotate_to_zero) {
+    QSV_RANGE("qsv_collapse");
     if (!s || (!qargs && m)) QSV_FAIL(QSV_ERR_INVALID, "qsv_collapse: NULL argument");
     QSV_CUDA(cudaSetDevice(s->device));
     QSV_TRY(qsv_materialize(const_cast<qsv_state*>(s)));

@@ -32,15 +32,17 @@ def main():
     cases.append(("qv20", 20, lib.quantum_volume(20, 8, seed=9)))      # several swaps ride inside fused passes
     cases.append(("su2_19", 19, lib.named_to_matrices(lib.efficient_su2_named(
         19, 2, np.random.default_rng(4).uniform(-3, 3, 2 * 19 * 3)))))
-    fused_seen = 0
-    # transports: 2 = peer memory with the swap carried by the next fused pass (default), 1 = peer memory,
-    # standalone exchange kernel, 0 = NCCL send/recv
-    for transport in (2, 1, 0):
+    fused_seen = {}
+    # transports: peer memory with the swap carried by a fused pass -- pushed by the last pass before it
+    # ("scatter", the default where it applies) or pulled by the first pass after it ("gather") --, peer
+    # memory with the standalone exchange kernel, and NCCL send/recv
+    variants = (("p2p+scatter", 1, 3), ("p2p+gather", 1, 1), ("p2p", 1, 0), ("nccl", 0, 0))
+    for label, p2p, fuse in variants:
         for name, n, gates in cases:
             sv = sharded_statevector(n, ctx)
             try:
-                sv.set_option("dist_p2p", 1 if transport else 0)
-                sv.set_option("dist_fuse_swap", 1 if transport == 2 else 0)
+                sv.set_option("dist_p2p", p2p)
+                sv.set_option("dist_fuse_swap", fuse)
             except NotImplementedError:
                 if rank == 0:
                     print("P2P transport unavailable (CUDA IPC); NCCL only", flush=True)
@@ -65,26 +67,25 @@ def main():
             slab = local_slab(sv)
             lo = rank << nl
             err = float(np.max(np.abs(slab - want[lo:lo + (1 << nl)])))
-            assert err < ATOL, (name, transport, err)
+            assert err < ATOL, (name, label, err)
             # bit-exact check on the engine's OWN amplitudes: every rank drops its slab in /tmp, the
             # norm all-reduce below doubles as the barrier, then each rank rebuilds the full state
-            tag = f"/tmp/qsv_dist_{ctx.port}_{name}_{transport}"
+            tag = f"/tmp/qsv_dist_{ctx.port}_{name}_{label}"
             np.save(f"{tag}_{rank}.npy", slab)
             sv._norm2()
             full = np.concatenate([np.load(f"{tag}_{r}.npy") for r in range(world)])
             idx_ref = ref.tree_choice_indices_sharded(ref.tree_probabilities(full), u, world)
             mism = int(np.sum(idx != idx_ref))
             assert mism == 0, (name, mism)
-            if transport == 2:
-                fused_seen += c["fused_swaps"]
+            if fuse:
+                fused_seen[label] = fused_seen.get(label, 0) + c["fused_swaps"]
             else:
                 assert c["fused_swaps"] == 0
             if rank == 0:
-                print(f"[{name} transport={('nccl', 'p2p', 'p2p+fused')[transport]}] amp err {err:.1e} swaps "
-                      f"{c['swap_count']} (fused {c['fused_swaps']}) passes {c['state_passes']} sample mismatches {mism}",
-                      flush=True)
+                print(f"[{name} transport={label}] amp err {err:.1e} swaps {c['swap_count']} (fused {c['fused_swaps']}) "
+                      f"passes {c['state_passes']} sample mismatches {mism}", flush=True)
             del sv
-    assert fused_seen > 0, "no swap was carried by a fused pass"
+    assert all(v > 0 for v in fused_seen.values()), f"no swap was carried by a fused pass: {fused_seen}"
     print(f"DIST_GPU_OK rank {rank} of {world}", flush=True)
 
 

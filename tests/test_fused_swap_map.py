@@ -21,7 +21,7 @@ from qiskit_b200 import circuit_library as lib
 from qiskit_b200.lowering import gate_list_to_stream
 
 
-def _emulate(n_local, lpos, a, arr, cnt):
+def _emulate(n_local, lpos, a, arr, cnt, mode=1):
     qsv = _lib.load()
     size = 1 << n_local
     src_j = np.zeros(size, dtype=np.uint32)
@@ -29,7 +29,7 @@ def _emulate(n_local, lpos, a, arr, cnt):
     tile_of = np.zeros(size, dtype=np.uint32)
     sig = np.zeros((size >> 12) * 16, dtype=np.uint32)
     nin, ok = C.c_int(), C.c_int()
-    _lib.check(qsv.qsv_debug_fused_swap(n_local, len(lpos), _lib.int_array(lpos), a, arr, cnt,
+    _lib.check(qsv.qsv_debug_fused_swap(mode, n_local, len(lpos), _lib.int_array(lpos), a, arr, cnt,
                                         src_j.ctypes.data, src_addr.ctypes.data, tile_of.ctypes.data,
                                         sig.ctypes.data, C.byref(nin), C.byref(ok)))
     return bool(ok.value), nin.value, src_j, src_addr, tile_of, sig.reshape(-1, 16)
@@ -58,8 +58,12 @@ CASES = [
 ]
 
 
+@pytest.mark.parametrize("mode", [1, 2, 3])
 @pytest.mark.parametrize("n_local,lpos,gq", CASES)
-def test_fused_swap_gather_map(n_local, lpos, gq):
+def test_fused_swap_remote_map(n_local, lpos, gq, mode):
+    """mode 1: gather (copy-in mapping of the first pass after the swap); modes 2 / 3: scatter through the
+    copy-out / direct-store mapping of the last pass before it.  The swap is an involution, so the same
+    three properties hold with "source" read as "destination"."""
     k = len(lpos)
     st = gate_list_to_stream(_gates_on(n_local, gq, seed=n_local + k))
     arr, cnt = st.to_c()
@@ -68,8 +72,10 @@ def test_fused_swap_gather_map(n_local, lpos, gq):
     lmask = sum(1 << p for p in lpos)
     per_rank = {}
     for a in range(1 << k):
-        ok, nin, src_j, src_addr, tile_of, sig = _emulate(n_local, lpos, a, arr, cnt)
-        assert ok, "first pass of the test stream must be a fused pass"
+        ok, nin, src_j, src_addr, tile_of, sig = _emulate(n_local, lpos, a, arr, cnt, mode)
+        if mode == 3 and not ok:
+            pytest.skip("the pass has no direct-store phase")
+        assert ok, "the pass of the test stream must be a fused pass"
         # 1. coverage (the emulator fails on double coverage; here: nothing left out)
         assert int(np.sum(tile_of == 0xFFFFFFFF)) == 0
         # 2. swap semantics
