@@ -82,6 +82,7 @@ struct qsv_state {
     size_t flush_bytes;
     // timer
     cudaEvent_t ev0, ev1;
+    cudaEvent_t tev0, tev1;  // QSV_TRACE per-pass timing (separate from the qsv_timer_begin / _end pair)
     // tunables
     int tile_bits;  // T: amplitudes per tile = 2^T
     int low_bits;   // L: lowest L index bits are always part of a tile (coalescing)

@@ -31,7 +31,8 @@
 #define FP_MAX_DIAGS 40  // diagonal ops per pass
 #define FP_NOCOEF 0xffffffffu
 
-enum { FP_D1C = 0, FP_D1R = 1, FP_D2C = 2, FP_D2R = 3, FP_DIAG = 4, FP_DIAGU = 5, FP_D1L = 6, FP_D1RY = 7, FP_D1H = 8, FP_D1HY = 9 };
+enum { FP_D1C = 0, FP_D1R = 1, FP_D2C = 2, FP_D2R = 3, FP_DIAG = 4, FP_DIAGU = 5, FP_D1L = 6, FP_D1RY = 7, FP_D1H = 8, FP_D1HY = 9,
+       FP_DIAGB = 10 };
 
 struct FpPhase {           // 80 bytes
     uint16_t rd[16];       // register r is read from byte offset (thread offset ^ rd[r]) of the tile buffer
@@ -149,6 +150,13 @@ struct FpRemote {
     // (measured: a B200 sustains ~340 GB/s of remote reads but about twice that of remote writes), and the
     // same handshake orders them: a rank signals that it has loaded tile i before anybody may overwrite it.
     // Direct-store phase: register r of thread t goes to rank j = j_tile | j_thread | st_jreg[r].
+    // Tile order.  The swapped bits outside the tile are high index bits, i.e. the top bits of the tile
+    // number: walked in plain order a rank would first do all its local tiles (links idle) and then all
+    // remote ones (links saturated, SMs waiting).  The tile COUNTER therefore has those bits exchanged
+    // with counter bits just above the grid size (tswap_hi[i] <-> tswap_lo[i]), so every CTA alternates
+    // between local and remote tiles.  The same bijection on every rank: counters still match.
+    int32_t ntswap;
+    uint8_t tswap_lo[FPR_MAXK], tswap_hi[FPR_MAXK];
     int8_t st_thr_bit[FPR_MAXK];         // [i]: direct-store thread bit (0..7) carrying swapped local bit i, or -1
     uint8_t st_jreg[16];                 // bits of j contributed by register r
     uint64_t st_clean[16];               // P.st_off[r] with the swapped bits cleared
@@ -159,6 +167,15 @@ __host__ __device__ __forceinline__ uint64_t fp_tile_base(const FpPass& P, uint3
     for (int sgm = 0; sgm < P.nseg; ++sgm)
         base |= (uint64_t)((tile >> P.seg_src[sgm]) & P.seg_mask[sgm]) << P.seg_dst[sgm];
     return base;
+}
+// tile counter -> tile number (see FpRemote::ntswap)
+__host__ __device__ __forceinline__ uint32_t fpr_tile_number(const FpRemote& R, uint32_t counter) {
+    uint32_t tnum = counter;
+    for (int i = 0; i < R.ntswap; ++i) {
+        const uint32_t x = ((tnum >> R.tswap_lo[i]) ^ (tnum >> R.tswap_hi[i])) & 1u;
+        tnum ^= (x << R.tswap_lo[i]) | (x << R.tswap_hi[i]);
+    }
+    return tnum;
 }
 // bits of j fixed by the tile (swapped local bits outside the tile)
 __host__ __device__ __forceinline__ uint32_t fpr_j_tile(const FpRemote& R, uint64_t tile_base) {
@@ -367,6 +384,62 @@ __device__ __forceinline__ void fp_diag(double2 (&v)[16], const FpPass& P, int d
     }
 }
 
+// v[r] *= c for the registers whose bit B is set
+template <int B>
+__device__ __forceinline__ void fp_mul_bit(double2 (&v)[16], const double2 c) {
+#pragma unroll
+    for (int r = 0; r < 16; ++r)
+        if (r & (1 << B)) fp_cmul_inplace(v[r], c);
+}
+__device__ __forceinline__ void fp_mul_bit_dyn(double2 (&v)[16], int b, const double2 c) {
+    switch (b) {
+        case 0: fp_mul_bit<0>(v, c); break;
+        case 1: fp_mul_bit<1>(v, c); break;
+        case 2: fp_mul_bit<2>(v, c); break;
+        default: fp_mul_bit<3>(v, c); break;
+    }
+}
+
+// FP_DIAGB, a "bilinear" phase table.  A product of controlled-phase / RZZ-like gates has a quadratic
+// log-phase, so its table over (register bits r, other bits o) factors as
+//     T[r, o] = T0[o] * U[r] * prod_{a in r} C_a[o]
+// (checked numerically on the host, entry by entry).  U is the uniform 16-entry factor (an FP_DIAGU op);
+// this op applies T0 and the C_a: the thread reads 1 + na CONSECUTIVE entries of row o instead of the 16
+// scattered 16-byte entries FP_DIAG needs, and spends 16 + 8 (na - 1) + 1 complex multiplications.
+// FpDiag fields reused: regpart[0] = na, regpart[1 + a] = register bit of factor a, regpart[5] = row stride.
+__device__ __forceinline__ void fp_diagb(double2 (&v)[16], const FpPass& P, int di, const uint16_t* __restrict__ tabs_sm,
+                                         uint64_t tile_base, uint32_t t) {
+    const FpDiag& d = P.diags[di];
+    uint32_t glob = 0;
+    for (int j = 0; j < d.nglob; ++j) glob |= (uint32_t)((tile_base >> d.gbit[j]) & 1ull) << d.gj[j];
+    const uint32_t row = tabs_sm[d.tab * FP_NT + t] | glob;
+    const double2* __restrict__ tab = P.gdata + d.table_off + row * d.regpart[5];
+    const int na = d.regpart[0];
+    const double2 c0 = __ldg(tab);
+    const double2 c1 = cmul(c0, __ldg(tab + 1));   // na >= 1 by construction
+    const int b0 = d.regpart[1];
+    // registers with bit b0 clear take T0, the others T0 * C_0: one multiplication per register
+    switch (b0) {
+        case 0:
+#pragma unroll
+            for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], (r & 1) ? c1 : c0);
+            break;
+        case 1:
+#pragma unroll
+            for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], (r & 2) ? c1 : c0);
+            break;
+        case 2:
+#pragma unroll
+            for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], (r & 4) ? c1 : c0);
+            break;
+        default:
+#pragma unroll
+            for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], (r & 8) ? c1 : c0);
+            break;
+    }
+    for (int a = 1; a < na; ++a) fp_mul_bit_dyn(v, d.regpart[1 + a], __ldg(tab + 1 + a));
+}
+
 __device__ __forceinline__ void fp_apply(double2 (&v)[16], const FpPass& P, int si, const uint16_t* __restrict__ tabs_sm,
                                          uint64_t tile_base, uint32_t t) {
     const int kind = P.subs[si].kind, b = P.subs[si].b, mo = P.subs[si].mat;
@@ -412,6 +485,7 @@ __device__ __forceinline__ void fp_apply(double2 (&v)[16], const FpPass& P, int 
             for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], make_double2(P.mats[mo + 2 * r], P.mats[mo + 2 * r + 1]));
             break;
         }
+        case FP_DIAGB * 16: fp_diagb(v, P, mo, tabs_sm, tile_base, t); break;
         default: fp_diag(v, P, mo, tabs_sm, tile_base, t); break;
     }
 }
@@ -469,7 +543,7 @@ __device__ __forceinline__ void fp_pass_body(double2* amp, const double2* src, c
     const uint64_t sst_clean = SCATTER ? (st_thread & ~R.lmask) : 0ull;
 
     auto tile_base_of = [&](uint32_t tile) {
-        const uint64_t base = fp_tile_base(P, tile);
+        const uint64_t base = fp_tile_base(P, REMOTE ? fpr_tile_number(R, tile) : tile);
         return REMOTE ? (base ^ R.out_xor) : base;
     };
     // REMOTE: rows [r0, r1) of a tile, gathered from the ranks that hold them, into `buf`

@@ -1611,6 +1611,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
     for (int b = 0; b < n && popc64(active) < FP_T; ++b) active |= 1ull << b;  // low bits first
     if (popc64(active) != FP_T) return QSV_OK;
     static const bool use_lifting = !getenv("QSV_NO_LIFT");
+    static const bool use_bilinear = !getenv("QSV_NO_BILINEAR");
     FpPass& P = out.P;
     memset(&P, 0, sizeof P);
     int local_of[64];
@@ -1983,6 +1984,101 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
                 }
             } else if (op.kind == CL_DIAG) {
                 if (tabs.size() / FP_NT >= FP_MAX_TABS || diags.size() >= FP_MAX_DIAGS) return QSV_OK;
+                // Bilinear factorisation (FP_DIAGB, qsv_fused.cuh): T[r, o] = T0[o] * U[r] * prod_{a in r} C_a[o].
+                // Holds for every product of controlled-phase / RZZ / RZ gates (QFT, Trotter steps); verified
+                // entry by entry, so any other table simply keeps the generic path below.
+                if (use_bilinear) {
+                    int rj[4], na = 0, oj[DIAG_MAX_BITS], no = 0;   // table index bits fed by register bits / by the rest
+                    for (int j = 0; j < op.k; ++j) {
+                        if (op.bits[j] < 64 && ((S >> op.bits[j]) & 1u)) rj[na++] = j;
+                        else oj[no++] = j;
+                    }
+                    bool ok_b = na >= 1 && na < op.k && std::abs(op.m[0]) > 0.5;
+                    const size_t nrow = (size_t)1 << no;
+                    std::vector<cplx> t0(nrow), ca((size_t)na * nrow), ureg((size_t)1 << na);
+                    auto full = [&](size_t rr, size_t oo) {   // table index from (register part, other part)
+                        size_t x = 0;
+                        for (int a = 0; a < na; ++a) x |= ((rr >> a) & 1) << rj[a];
+                        for (int b = 0; b < no; ++b) x |= ((oo >> b) & 1) << oj[b];
+                        return x;
+                    };
+                    for (size_t oo = 0; oo < nrow && ok_b; ++oo) {
+                        t0[oo] = op.m[full(0, oo)];
+                        ok_b = std::abs(t0[oo]) > 0.5;
+                        for (int a = 0; a < na && ok_b; ++a) ca[(size_t)a * nrow + oo] = op.m[full((size_t)1 << a, oo)] / t0[oo];
+                    }
+                    for (size_t rr = 0; rr < ureg.size() && ok_b; ++rr) {
+                        cplx den = t0[0];
+                        for (int a = 0; a < na; ++a)
+                            if ((rr >> a) & 1) den *= ca[(size_t)a * nrow];
+                        ureg[rr] = op.m[full(rr, 0)] / den;
+                    }
+                    for (size_t rr = 0; rr < ureg.size() && ok_b; ++rr)
+                        for (size_t oo = 0; oo < nrow && ok_b; ++oo) {
+                            cplx model = t0[oo] * ureg[rr];
+                            for (int a = 0; a < na; ++a)
+                                if ((rr >> a) & 1) model *= ca[(size_t)a * nrow + oo];
+                            ok_b = std::abs(model - op.m[full(rr, oo)]) <= 2e-14;
+                        }
+                    bool u_trivial = true;
+                    for (const cplx& u : ureg) u_trivial &= std::abs(u - cplx(1.0, 0.0)) <= 1e-15;
+                    if (ok_b && (u_trivial || (nsubs + 1 < FP_MAX_SUBS && nmat + 32 <= FP_MAX_MAT && cnt < 254))) {
+                        if (!u_trivial) {   // the register-only factor: 16 uniform coefficients
+                            FpSub& su = P.subs[nsubs];
+                            memset(&su, 0, sizeof su);
+                            su.kind = FP_DIAGU;
+                            su.mat = (uint16_t)nmat;
+                            for (int r = 0; r < 16; ++r) {
+                                size_t rr = 0;
+                                for (int a = 0; a < na; ++a) rr |= (size_t)((r >> rank_in(S, op.bits[rj[a]])) & 1) << a;
+                                P.mats[nmat++] = ureg[rr].real();
+                                P.mats[nmat++] = ureg[rr].imag();
+                            }
+                            ++nsubs;
+                            ++cnt;
+                        }
+                        FpSub& sb2 = P.subs[nsubs];
+                        memset(&sb2, 0, sizeof sb2);
+                        FpDiag d;
+                        memset(&d, 0, sizeof d);
+                        d.table_off = (uint32_t)gdata.size();
+                        d.tab = (uint16_t)(tabs.size() / FP_NT);
+                        d.regpart[0] = (uint16_t)na;
+                        for (int a = 0; a < na; ++a) d.regpart[1 + a] = (uint16_t)rank_in(S, op.bits[rj[a]]);
+                        d.regpart[5] = (uint16_t)(1 + na);
+                        uint32_t tb[DIAG_MAX_BITS];
+                        for (int b = 0; b < no; ++b) {
+                            tb[b] = 0xffffffffu;
+                            const int bit = op.bits[oj[b]];
+                            if (bit >= 64) {
+                                d.gbit[d.nglob] = (uint8_t)(bit - 64);
+                                d.gj[d.nglob] = (uint8_t)b;
+                                ++d.nglob;
+                            } else {
+                                tb[b] = (uint32_t)bit;
+                            }
+                        }
+                        for (int t = 0; t < FP_NT; ++t) {
+                            uint32_t thr = 0;
+                            for (int b = 0; b < no; ++b)
+                                if (tb[b] != 0xffffffffu) thr |= ((base_of[t] >> tb[b]) & 1u) << b;
+                            tabs.push_back((uint16_t)thr);
+                        }
+                        for (size_t oo = 0; oo < nrow; ++oo) {
+                            gdata.push_back(make_double2(t0[oo].real(), t0[oo].imag()));
+                            for (int a = 0; a < na; ++a) {
+                                const cplx c = ca[(size_t)a * nrow + oo];
+                                gdata.push_back(make_double2(c.real(), c.imag()));
+                            }
+                        }
+                        sb2.kind = FP_DIAGB;
+                        sb2.mat = (uint16_t)diags.size();
+                        diags.push_back(d);
+                        ++nsubs;
+                        ++cnt;
+                        continue;
+                    }
+                }
                 FpDiag d;
                 memset(&d, 0, sizeof d);
                 d.table_off = (uint32_t)gdata.size();
@@ -2133,7 +2229,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
 }
 
 static void trace_fused_pass(const FpPass& P, FILE* f) {
-    int cnt[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    int cnt[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     fprintf(f, "[fused] T bits:");
     for (int b = 0; b < FP_T; ++b) fprintf(f, " %d", P.pos[b]);
     fprintf(f, " | %sphases %d:", P.warp_local ? "warp-local " : "", P.nphases);
@@ -2142,8 +2238,8 @@ static void trace_fused_pass(const FpPass& P, FILE* f) {
                 P.phases[p].rcoef != FP_NOCOEF ? "r" : "", P.phases[p].wcoef != FP_NOCOEF ? "w" : "");
         for (int i = 0; i < P.phases[p].nsub; ++i) cnt[P.subs[P.phases[p].sub_first + i].kind]++;
     }
-    fprintf(f, " | d1c %d d1r %d d1l %d d1ry %d d1h %d d2c %d d2r %d diag %d diagu %d | tabs %d\n", cnt[0], cnt[1], cnt[6],
-            cnt[7], cnt[8] + cnt[9], cnt[2], cnt[3], cnt[4], cnt[5], P.ntabs);
+    fprintf(f, " | d1c %d d1r %d d1l %d d1ry %d d1h %d d2c %d d2r %d diag %d diagb %d diagu %d | tabs %d\n", cnt[0], cnt[1],
+            cnt[6], cnt[7], cnt[8] + cnt[9], cnt[2], cnt[3], cnt[4], cnt[10], cnt[5], P.ntabs);
 }
 
 static int upload_product_tables(qsv_state* s, uint64_t neutral, const std::vector<cplx>& extra);
@@ -2193,6 +2289,31 @@ static void build_fp_remote(const FpPass& P, const QsvPendingSwap& W, FpRemote& 
         }
         R.jrow[r] = (uint8_t)jr;
         R.row_clean[r] = clean * sizeof(double2);
+    }
+    // tile order: bring the tile-number bits of the non-tile swapped positions down to counter bits 9, 10, ...
+    // (just above the grid of 2 x 148 CTAs) so that local and remote tiles alternate within every CTA
+    {
+        int ntbits = 0;
+        while ((1u << ntbits) < P.ntiles) ++ntbits;
+        int lo = 9;
+        for (int i = 0; i < R.nout; ++i) {
+            int q = 0;  // tile-number bit of index bit out_pos[i] = non-tile index bits below it
+            for (int b = 0; b < R.out_pos[i]; ++b)
+                if (tile_bit_of[b] < 0) ++q;
+            if (q <= lo || lo >= ntbits) continue;
+            bool clash = false;  // `lo` must not itself be the home of another swapped bit
+            for (int i2 = 0; i2 < R.nout; ++i2) {
+                int q2 = 0;
+                for (int b = 0; b < R.out_pos[i2]; ++b)
+                    if (tile_bit_of[b] < 0) ++q2;
+                clash |= q2 == lo;
+            }
+            if (clash) { ++lo; --i; continue; }
+            R.tswap_lo[R.ntswap] = (uint8_t)lo;
+            R.tswap_hi[R.ntswap] = (uint8_t)q;
+            ++R.ntswap;
+            ++lo;
+        }
     }
     // scatter mode, direct-store phase: the same decomposition for the store mapping
     for (int i = 0; i < W.k; ++i) {
@@ -2274,7 +2395,7 @@ static int launch_fused_pass(qsv_state* s, const FusedBuilt& fb, bool is_last) {
     }
     static const bool trace = getenv("QSV_TRACE") != nullptr;
     if (trace) trace_fused_pass(P, stderr);
-    if (trace) QSV_CUDA(cudaEventRecord(s->ev0, s->stream));
+    if (trace) QSV_CUDA(cudaEventRecord(s->tev0, s->stream));
     const double2* src = s->read_from ? s->read_from : s->amp;
     s->read_from = nullptr;  // only the first pass after the request reads the other buffer
     if (s->prod_pending && (s->use_fused3 || !s->use_product_fold)) QSV_TRY(qsv_flush_product(s));
@@ -2305,9 +2426,9 @@ static int launch_fused_pass(qsv_state* s, const FusedBuilt& fb, bool is_last) {
         QSV_CUDA(cudaGetLastError());
         if (trace) {
             float ms = 0.f;
-            QSV_CUDA(cudaEventRecord(s->ev1, s->stream));
-            QSV_CUDA(cudaEventSynchronize(s->ev1));
-            QSV_CUDA(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+            QSV_CUDA(cudaEventRecord(s->tev1, s->stream));
+            QSV_CUDA(cudaEventSynchronize(s->tev1));
+            QSV_CUDA(cudaEventElapsedTime(&ms, s->tev0, s->tev1));
             fprintf(stderr, "        -> %.3f ms\n", ms);
         }
         s->ctr.kernel_launches++;
@@ -2332,9 +2453,9 @@ static int launch_fused_pass(qsv_state* s, const FusedBuilt& fb, bool is_last) {
     QSV_CUDA(cudaGetLastError());
     if (trace) {
         float ms = 0.f;
-        QSV_CUDA(cudaEventRecord(s->ev1, s->stream));
-        QSV_CUDA(cudaEventSynchronize(s->ev1));
-        QSV_CUDA(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+        QSV_CUDA(cudaEventRecord(s->tev1, s->stream));
+        QSV_CUDA(cudaEventSynchronize(s->tev1));
+        QSV_CUDA(cudaEventElapsedTime(&ms, s->tev0, s->tev1));
         fprintf(stderr, "        -> %.3f ms\n", ms);
     }
     s->ctr.kernel_launches++;
@@ -2824,7 +2945,7 @@ extern "C" int qsv_debug_fused_swap(int mode, int n_local, int k, const int* lpo
     const uint64_t count = 1ull << n_local;
     for (uint64_t x = 0; x < count; ++x) tile_of[x] = 0xffffffffu;
     for (uint32_t tile = 0; tile < P->ntiles; ++tile) {
-        const uint64_t base = fp_tile_base(*P, tile) ^ R.out_xor;
+        const uint64_t base = fp_tile_base(*P, fpr_tile_number(R, tile)) ^ R.out_xor;
         const uint32_t jt = fpr_j_tile(R, base);
         for (uint32_t x = 0; x < 16; ++x) sig[(size_t)tile * 16 + x] = x < (1u << R.nin) ? fpr_signal_peer(R, jt, x) : 0xffffffffu;
         for (uint32_t t = 0; t < FP_NT && mode == 3; ++t) {   // scatter through the direct-store mapping

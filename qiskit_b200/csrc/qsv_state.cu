@@ -151,6 +151,8 @@ int qsv_state_alloc(qsv_state** out, int n_qubits, int n_local, int device, cuda
     }
     QSV_CUDA(cudaEventCreate(&s->ev0));
     QSV_CUDA(cudaEventCreate(&s->ev1));
+    QSV_CUDA(cudaEventCreate(&s->tev0));
+    QSV_CUDA(cudaEventCreate(&s->tev1));
     cudaDeviceProp prop;
     QSV_CUDA(cudaGetDeviceProperties(&prop, device));
     s->num_sms = prop.multiProcessorCount;
@@ -197,6 +199,8 @@ extern "C" int qsv_destroy(qsv_state* s) {
     if (s->pinned) cudaFreeHost(s->pinned);
     cudaEventDestroy(s->ev0);
     cudaEventDestroy(s->ev1);
+    cudaEventDestroy(s->tev0);
+    cudaEventDestroy(s->tev1);
     if (s->owns_stream) cudaStreamDestroy(s->stream);
     delete s;
     return QSV_OK;

@@ -19,7 +19,7 @@ from qiskit_b200.lowering import gate_list_to_stream
 from qiskit_b200.pauli import pauli_masks
 
 mode = sys.argv[1] if len(sys.argv) > 1 else "su2"
-n = int(sys.argv[2]) if len(sys.argv) > 2 else {"su2": 28, "stream": 30, "sampler": 30}[mode]
+n = int(sys.argv[2]) if len(sys.argv) > 2 else {"su2": 28, "stream": 30, "sampler": 30, "qft": 30, "tfim": 32, "qv": 30}[mode]
 qsv = _lib.load()
 _lib.require_device()
 sv = Statevector.from_int(0, 1 << n)
@@ -81,3 +81,17 @@ elif mode == "sampler":
         timed(lambda: _lib.check(qsv.qsv_sample(h, None, n, u.ctypes.data, u.size, idx.ctypes.data,
                                                  C.byref(total))), f"[{it}] sample 1e6 shots")
     print("total =", total.value, "idx[:4] =", idx[:4])
+elif mode in ("qft", "tfim", "qv"):
+    # one benchmark stream, timed twice (QSV_TRACE=1 prints the per-pass plan and times)
+    if mode == "qft":
+        gl = lib.named_to_matrices(lib.qft_named(n))
+    elif mode == "tfim":
+        gl = lib.named_to_matrices(lib.tfim_named(n, steps=10))
+    else:
+        gl = lib.quantum_volume(n, 4, seed=0)
+    st = gate_list_to_stream(gl)
+    arr, cnt = st.to_c()
+    for it in range(2):
+        _lib.check(qsv.qsv_init_basis(h, 0))
+        timed(lambda: _lib.check(qsv.qsv_apply_gates(h, arr, cnt, 0)), f"[{it}] {mode} {n}q {cnt} gates")
+    print("norm - 1 =", sv._norm2() - 1.0)

@@ -55,6 +55,7 @@ CASES = [
     (17, [16, 9, 5], [16, 12, 9, 13, 11, 10]),          # k=3, row bit + thread bits (5 fills the low tile bits)
     (17, [14, 15, 16], [6, 7, 8, 10]),                  # k=3, all out
     (14, [13, 12], [13, 2, 12, 1]),                     # small slab: 4 tiles
+    (24, [23, 22], [5, 6, 7, 8]),                       # 4096 tiles: the tile counter's bits are permuted
 ]
 
 
