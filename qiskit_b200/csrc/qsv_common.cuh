@@ -150,6 +150,8 @@ int qsv_dist_flush_swap(qsv_state* s);                    // run a pending swap 
 int qsv_dist_fused_swap_begin(qsv_state* s, uint32_t signals_per_tile, uint32_t* target_out);  // (gather: barrier) + timer start
 int qsv_dist_fused_swap_end(qsv_state* s);                // (scatter: barrier), timer stop, counters, handshake error check
 
+int qsv_fused_identity_pass(qsv_state* s);               // qsv_gate.cu: gate-less scatter pass = the exchange itself
+
 int qsv_materialize(qsv_state* s);  // write a pending |index> into the amplitude buffer
 int qsv_flush_product(qsv_state* s);  // write a pending product state into the amplitude buffer (qsv_gate.cu)
 int qsv_ensure_scratch(qsv_state* s, size_t bytes);

@@ -98,6 +98,7 @@ struct qsv_dist {
     void* ipc_flag_base[MAX_RANKS];
     uint32_t flag_target;          // identical on every rank: all ranks run the same fused swap passes
     int use_fuse;                  // option "dist_fuse_swap"
+    int use_push;                  // option "dist_push_swap": standalone exchanges as gate-less scatter passes
     QsvPendingSwap pending;        // storage behind qsv_state::pending_swap
     int pending_gpos[MAX_G], pending_k;
     cudaEvent_t fused_e0;
@@ -283,6 +284,8 @@ extern "C" int qsv_create_dist(qsv_state** out, int n_qubits, int device, int ra
         // bit 0: gather (first pass after the swap pulls), bit 1: scatter (last pass before it pushes; preferred)
         const char* fenv = getenv("QSV_DIST_FUSE_SWAP");
         d->use_fuse = d->p2p ? (fenv && *fenv ? atoi(fenv) & 3 : 3) : 0;
+        const char* penv = getenv("QSV_DIST_PUSH_SWAP");
+        d->use_push = penv && *penv ? atoi(penv) != 0 : 1;
     } while (0);
     if (rc != QSV_OK) {
         std::string msg = qsv_last_error();
@@ -313,6 +316,10 @@ int qsv_dist_set_option(qsv_state* s, const char* name, int64_t value) {
     if (!strcmp(name, "dist_fuse_swap")) {
         if (value && !s->dist->p2p) QSV_FAIL(QSV_ERR_UNSUPPORTED, "peer slabs are not mapped (CUDA IPC unavailable)");
         s->dist->use_fuse = (int)(value & 3);  // 0 off, 1 gather, 2 scatter, 3 both (scatter where it applies)
+        return QSV_OK;
+    }
+    if (!strcmp(name, "dist_push_swap")) {
+        s->dist->use_push = value != 0;
         return QSV_OK;
     }
     if (!strcmp(name, "dist_min_lpos")) {
@@ -510,7 +517,22 @@ static int swap_execute(qsv_state* s, int k, const int* gpos, const int* lpos) {
     return QSV_OK;
 }
 
+static int swap_defer(qsv_state* s, int k, const int* gpos, const int* lpos, int mode);
+
+// The standalone exchange.  Preferred: a gate-less scatter pass (remote writes only, same handshake as
+// the fused swap passes); otherwise the pairwise in-place kernel / the NCCL transport.
 static int dist_swap_bits(qsv_state* s, int k, const int* gpos, const int* lpos) {
+    qsv_dist* d = s->dist;
+    if (d->use_p2p && (d->use_fuse & 2) && d->use_push && s->n_local >= 12 && !s->pending_swap) {
+        QSV_TRY(swap_defer(s, k, gpos, lpos, 2));
+        QSV_TRY(qsv_fused_identity_pass(s));
+        if (!s->pending_swap) {  // carried
+            s->ctr.fused_swaps--;  // counted as an exchange of its own, not as one that rode inside a gate pass
+            swap_commit_perm(s, k, gpos, lpos);
+            return QSV_OK;
+        }
+        s->pending_swap = nullptr;
+    }
     QSV_TRY(swap_execute(s, k, gpos, lpos));
     swap_commit_perm(s, k, gpos, lpos);
     return QSV_OK;

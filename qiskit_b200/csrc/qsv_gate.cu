@@ -1611,7 +1611,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
     for (int b = 0; b < n && popc64(active) < FP_T; ++b) active |= 1ull << b;  // low bits first
     if (popc64(active) != FP_T) return QSV_OK;
     static const bool use_lifting = !getenv("QSV_NO_LIFT");
-    static const bool use_bilinear = !getenv("QSV_NO_BILINEAR");
+    static const bool use_bilinear = getenv("QSV_BILINEAR") && atoi(getenv("QSV_BILINEAR"));  // measured slower (profiles/r2_bilinear_tables_ab.txt): opt-in
     FpPass& P = out.P;
     memset(&P, 0, sizeof P);
     int local_of[64];
@@ -1720,6 +1720,13 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
             }
             sels.push_back(std::move(ps));
         }
+    }
+    if (sels.empty() && plan.gate_ids.empty()) {
+        // a pass without gates: one empty phase (registers loaded and stored unchanged).  Used as the
+        // standalone qubit exchange of sharded states (qsv_fused_identity_pass: a scatter pass with no arithmetic)
+        PhaseSel ps;
+        ps.S = 0;
+        sels.push_back(std::move(ps));
     }
     if (sels.empty() || sels.size() > FP_MAX_PHASES) return QSV_OK;
     // Warp-local passes: three tile bits that no dense / permutation op of the pass touches become
@@ -2460,6 +2467,41 @@ static int launch_fused_pass(qsv_state* s, const FusedBuilt& fb, bool is_last) {
     }
     s->ctr.kernel_launches++;
     s->ctr.state_passes++;
+    return QSV_OK;
+}
+
+// One fused pass with no gates over the low 12 index bits.  With a pending scatter swap it IS the
+// standalone global<->local qubit exchange: every tile is loaded from the own slab and stored into the
+// slabs that own it afterwards -- remote WRITES only (k_swap_p2p also reads remotely, and remote reads
+// cap at ~340 GB/s per GPU on this machine).  Returns with s->pending_swap still set when the pass
+// could not be built (the caller falls back to k_swap_p2p).
+int qsv_fused_identity_pass(qsv_state* s) {
+    if (!s->pending_swap || s->pending_swap->mode != 2 || s->n_local < FP_T) return QSV_OK;
+    std::vector<HGate> none;
+    PassPlan plan;
+    plan.qmask = 0;
+    std::vector<char> stage;
+    FusedBuilt fb;
+    bool ok = false;
+    const uint64_t phases_before = s->ctr.phases;
+    QSV_TRY(build_fused_pass(s, none, plan, stage, fb, ok));
+    s->ctr.phases = phases_before;
+    if (!ok) return QSV_OK;
+    const size_t used = stage.size();
+    if (used) {
+        QSV_TRY(qsv_ensure_scratch(s, used + 256));
+        QSV_TRY(qsv_ensure_pinned(s, used + 256));
+        QSV_CUDA(cudaStreamSynchronize(s->stream));
+        memcpy(s->pinned, stage.data(), used);
+        QSV_CUDA(cudaMemcpyAsync(s->scratch, s->pinned, used, cudaMemcpyHostToDevice, s->stream));
+        s->ctr.h2d_bytes += used;
+    }
+    fb.P.tabs = (const uint16_t*)((char*)s->scratch + fb.tabs_off);
+    fb.P.gdata = (const double2*)((char*)s->scratch + fb.gdata_off);
+    if (!fused_swap_capable(s, fb.P)) return QSV_OK;
+    const uint64_t passes_before = s->ctr.state_passes;
+    QSV_TRY(launch_fused_swap_pass(s, fb.P));
+    s->ctr.state_passes = passes_before;  // an exchange, not a gate pass
     return QSV_OK;
 }
 

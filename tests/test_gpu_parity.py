@@ -718,3 +718,17 @@ def test_edge_cases_small_and_empty():
     with pytest.raises(TypeError):
         StatevectorSampler().run([qm], shots=1.5).result()
     assert sum(StatevectorSampler(seed=1).run([qm], shots=1).result()[0].data.meas.get_counts().values()) == 1
+
+
+def test_kernel_matrix_with_bilinear_tables_opt_in():
+    """FP_DIAGB (bilinear phase tables) is opt-in (measured slower, profiles/r2_bilinear_tables_ab.txt) and read
+    from the environment once per process: the small-n kernel matrix (QFT / TFIM-like tables with register,
+    thread and off-tile bits, all checked against the oracle) runs in a child process with QSV_BILINEAR=1."""
+    import subprocess
+    import sys
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, QSV_BILINEAR="1")
+    res = subprocess.run([sys.executable, os.path.join(root, "scripts", "sanitize_matrix.py")], env=env,
+                         capture_output=True, text=True, timeout=900, cwd=root)
+    assert res.returncode == 0 and "sanitize matrix ok" in res.stdout, res.stdout[-2000:] + res.stderr[-2000:]
