@@ -634,11 +634,16 @@ __device__ __forceinline__ void fp_pass_body(double2* amp, const double2* src, c
             }
             if (ph.direct) {
                 // every thread has its registers: the buffer can take the next tile now
-                if (REMOTE && t == 0) fpr_wait(R, tile);  // ... and the peers have read what this tile overwrites
                 __syncthreads();
                 if (has_next) {
                     if (GATHER) finish_remote_load(next_base);
                     else issue_load(next_base);
+                }
+                if (REMOTE) {
+                    // the next tile is on its way while thread 0 waits for the peers to have read what
+                    // this tile overwrites (one NVLink latency when the pass has no arithmetic to hide it)
+                    if (t == 0) fpr_wait(R, tile);
+                    __syncthreads();
                 }
             }
             if (ph.rcoef != FP_NOCOEF) {

@@ -1,0 +1,14 @@
+# Round-2 profile: (1) plain bench, (2) ncu launch list of the SAME command, (3) --set full over one SU2 evaluation's
+# fused passes, (4) over a 30 q QuantumVolume stream, (5) over the expval kernels.  Numbers printed under ncu are never bench values.
+O=gpurun_out/${1:-ncu_r2}; mkdir -p $O
+CMD="python bench.py --steps 2 --warmup 3 --skip-sharded"
+timeout 900 $CMD > $O/bench_plain.json 2> $O/bench_plain.err; echo "plain bench exit $?"
+timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches_bench.csv \
+  $CMD > $O/bench_under_ncu.log 2>&1; echo "ncu launch list exit $?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_fused_pass -s 12 -c 12 \
+  -o $O/su2_fused -f python scripts/profile_run.py su2 > $O/ncu_su2.log 2>&1; echo "ncu fused exit $?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_fused_pass -s 11 -c 10 \
+  -o $O/qv30_fused -f python scripts/profile_run.py qv > $O/ncu_qv.log 2>&1; echo "ncu qv exit $?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_expval -s 3 -c 3 \
+  -o $O/su2_expval -f python scripts/profile_run.py su2 > $O/ncu_expval.log 2>&1; echo "ncu expval exit $?"
+ls -la $O
