@@ -232,7 +232,7 @@ int qsv_timer_end(qsv_state* s, float* ms_out);
 /* engine tunables, by name; for experiments and A/B measurements, the defaults are the product:
  *   tile_bits, low_bits, tile_threads      tile geometry of the unfused tile pass
  *   use_direct, use_cluster, use_fused     which kernel takes a pass (k_direct*, k_cluster_pass, k_fused_pass)
- *   direct_store, warp_local, fused3, linear_perm, diag_split   k_fused_pass variants
+ *   direct_store, warp_local, linear_perm, diag_split   k_fused_pass variants
  *   lazy_init, product_init, product_fold  deferred |index>, product-state prologue, prologue folded
  *                                          into the first fused pass
  *   dist_p2p, dist_fuse_swap, dist_min_lpos  sharded states: peer-memory transport, swap carried by the

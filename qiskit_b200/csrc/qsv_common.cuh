@@ -94,7 +94,6 @@ struct qsv_state {
     int use_warp_local;    // k_fused_pass: warp-private sub-tiles when three tile bits stay untouched
     int use_linear_perm;   // fused pass: X/CX/SWAP-like permutations are absorbed by the tile-index -> slot map
     int use_diag_split;    // fused pass: separable diagonal tables -> uniform register factor + one lookup per thread
-    int use_fused3;        // fused passes through k_fused_pass3 (one CTA per SM, two groups, three tile buffers)
     int num_sms;
     qsv_counters ctr;
     // sharding

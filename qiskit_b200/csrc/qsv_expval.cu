@@ -468,7 +468,6 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
             aux->use_fused = s->use_fused;
             aux->use_direct_store = s->use_direct_store;
             aux->use_warp_local = s->use_warp_local;
-            aux->use_fused3 = s->use_fused3;
             aux->use_linear_perm = s->use_linear_perm;
             aux->use_diag_split = s->use_diag_split;
             aux->lazy_init = 0;

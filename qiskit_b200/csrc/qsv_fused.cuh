@@ -731,161 +731,6 @@ __global__ void __launch_bounds__(FP_NT, 2) k_fused_swap_pass(double2* amp, cons
     fp_pass_body<MODE>(amp, amp, P, R);
 }
 
-// ---- k_fused_pass3: the same pass with THREE tile buffers per SM --------------------------------
-//
-// ncu on k_fused_pass (profiles/r1_ncu_fused_v2.txt): DRAM 53 %, FP64 pipe 30 %, issue slots 41 %,
-// 16 resident warps -- nothing saturated.  Each of the two CTAs of an SM owns ONE buffer, so the next
-// tile can only be requested once the current one has left the buffer (last phase); for the rest
-// of the tile's life that CTA has no load in flight.  Here one CTA per SM runs two independent
-// 256-thread groups (named barriers 1 and 2, never __syncthreads after the prologue) over three
-// buffers: the group that finds the spare buffer free takes it as soon as its own tile has landed
-// and streams its NEXT tile into it during all of its phases; when it is done with the current
-// buffer that one becomes the spare and the other group picks it up at its next phase boundary.
-// Ownership moves through one shared word (atomicExch by thread 0 of a group, published to the
-// group by the barrier that already separates the phases).
-#define FP3_NT 512
-#define FP3_NONE (-1)
-
-__device__ __forceinline__ void fp3_bar(uint32_t g) {
-    asm volatile("bar.sync %0, %1;\n" ::"r"(g + 1u), "r"(FP_NT) : "memory");
-}
-
-__global__ void __launch_bounds__(FP3_NT, 1) k_fused_pass3(double2* amp, const double2* src, const __grid_constant__ FpPass P) {
-    extern __shared__ __align__(16) unsigned char fp_smem[];
-    uint16_t* const tabs_sm = reinterpret_cast<uint16_t*>(fp_smem + 3 * FP_TILE * sizeof(double2));
-    // ctrl[0] = spare buffer (or FP3_NONE); ctrl[1 + 2 g + parity] = answer to group g's poll
-    int* const ctrl = reinterpret_cast<int*>(fp_smem + 3 * FP_TILE * sizeof(double2) + (size_t)P.ntabs * FP_NT * sizeof(uint16_t));
-    const uint32_t g = threadIdx.x >> 8, t = threadIdx.x & (FP_NT - 1);
-
-    for (int i = threadIdx.x; i < P.ntabs * (FP_NT / 2); i += FP3_NT)
-        reinterpret_cast<uint32_t*>(tabs_sm)[i] = __ldg(reinterpret_cast<const uint32_t*>(P.tabs) + i);
-    if (threadIdx.x == 0) ctrl[0] = 2;
-    __syncthreads();
-
-    uint64_t cp_off = 0;
-#pragma unroll
-    for (int b = 0; b < 8; ++b) cp_off |= (uint64_t)((t >> b) & 1u) << P.pos[b];
-    const uint32_t st16 = fp_swz(t) << 4;
-    uint64_t st_thread = 0;
-#pragma unroll
-    for (int b = 0; b < 8; ++b) st_thread |= (uint64_t)((t >> b) & 1u) << P.pos[P.st_tpos[b]];
-
-    auto tile_base_of = [&](uint32_t tile) {
-        uint64_t base = 0;
-        for (int sgm = 0; sgm < P.nseg; ++sgm)
-            base |= (uint64_t)((tile >> P.seg_src[sgm]) & P.seg_mask[sgm]) << P.seg_dst[sgm];
-        return base;
-    };
-    const uint32_t smem0 = (uint32_t)__cvta_generic_to_shared(fp_smem);
-    auto issue_load = [&](int buf, uint64_t tile_base) {
-        const char* gp = reinterpret_cast<const char*>(src + tile_base + cp_off);
-        const uint32_t dst0 = smem0 + (uint32_t)buf * (uint32_t)(FP_TILE * sizeof(double2));
-#pragma unroll
-        for (int r = 0; r < 16; ++r) {
-            const uint32_t dst = dst0 + (st16 ^ (fp_swz((uint32_t)r << 8) << 4));
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst), "l"(gp + P.row_off[r]));
-        }
-        asm volatile("cp.async.commit_group;\n" ::: "memory");
-    };
-    auto release = [&](int buf) {  // after a group barrier: nobody of this group touches buf any more
-        if (t == 0) {
-            __threadfence_block();
-            atomicExch(&ctrl[0], buf);
-        }
-    };
-
-    uint32_t tile = blockIdx.x * 2 + g;
-    if (tile >= P.ntiles) return;
-    const uint32_t stride = gridDim.x * 2;
-    int cur = (int)g, nxt = FP3_NONE;
-    uint32_t polls = 0;
-    uint64_t tile_base = tile_base_of(tile);
-    issue_load(cur, tile_base);
-    while (true) {
-        const uint32_t next = tile + stride;
-        const bool has_next = next < P.ntiles;
-        const uint64_t next_base = has_next ? tile_base_of(next) : 0;
-        const uint64_t diag_base = tile_base | P.index_base;
-        unsigned char* const tilebuf = fp_smem + (size_t)cur * (FP_TILE * sizeof(double2));
-        asm volatile("cp.async.wait_group 0;\n" ::: "memory");
-        bool want = has_next;  // still looking for a buffer to prefetch into
-        if (want && t == 0) ctrl[1 + 2 * g + (polls & 1u)] = atomicExch(&ctrl[0], FP3_NONE);
-        fp3_bar(g);  // tile visible to the group; poll answer published
-        if (want) {
-            nxt = *reinterpret_cast<volatile int*>(&ctrl[1 + 2 * g + (polls & 1u)]);
-            ++polls;
-            if (nxt != FP3_NONE) {
-                issue_load(nxt, next_base);
-                want = false;
-            }
-        }
-        bool stored = false;
-#pragma unroll 1
-        for (int p = 0; p < P.nphases; ++p) {
-            const FpPhase& ph = P.phases[p];
-            const uint32_t sb = (uint32_t)tabs_sm[ph.tab * FP_NT + t] << 4;
-            double2 v[16];
-#pragma unroll
-            for (int r = 0; r < 16; ++r) v[r] = *reinterpret_cast<const double2*>(tilebuf + (sb ^ ph.rd[r]));
-            if (ph.direct) {
-                fp3_bar(g);  // every thread of the group has its registers
-                if (has_next) {
-                    if (nxt != FP3_NONE) release(cur);
-                    else issue_load(cur, next_base);
-                }
-            }
-            if (ph.rcoef != FP_NOCOEF) {
-                const double2* __restrict__ c = P.gdata + ph.rcoef;
-#pragma unroll
-                for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], __ldg(c + r));
-            }
-            const int s0 = ph.sub_first, s1 = s0 + ph.nsub;
-#pragma unroll 1
-            for (int si = s0; si < s1; ++si) fp_apply(v, P, si, tabs_sm, diag_base, t);
-            if (ph.wcoef != FP_NOCOEF) {
-                const double2* __restrict__ c = P.gdata + ph.wcoef;
-#pragma unroll
-                for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], __ldg(c + r));
-            }
-            if (ph.direct) {
-                char* gp = reinterpret_cast<char*>(amp + tile_base + st_thread);
-#pragma unroll
-                for (int r = 0; r < 16; ++r) *reinterpret_cast<double2*>(gp + P.st_off[r]) = v[r];
-                stored = true;
-            } else {
-#pragma unroll
-                for (int r = 0; r < 16; ++r) *reinterpret_cast<double2*>(tilebuf + (sb ^ ph.wr[r])) = v[r];
-                if (want && t == 0) ctrl[1 + 2 * g + (polls & 1u)] = atomicExch(&ctrl[0], FP3_NONE);
-                fp3_bar(g);
-                if (want) {
-                    nxt = *reinterpret_cast<volatile int*>(&ctrl[1 + 2 * g + (polls & 1u)]);
-                    ++polls;
-                    if (nxt != FP3_NONE) {
-                        issue_load(nxt, next_base);
-                        want = false;
-                    }
-                }
-            }
-        }
-        if (!stored) {
-            const uint32_t so16 = P.out_tab == 0xffff ? st16 : ((uint32_t)tabs_sm[P.out_tab * FP_NT + t] << 4);
-            char* gp = reinterpret_cast<char*>(amp + tile_base + cp_off);
-#pragma unroll
-            for (int r = 0; r < 16; ++r)
-                *reinterpret_cast<double2*>(gp + P.row_off[r]) =
-                    *reinterpret_cast<const double2*>(tilebuf + (so16 ^ P.out_row[r]));
-            fp3_bar(g);
-            if (has_next) {
-                if (nxt != FP3_NONE) release(cur);
-                else issue_load(cur, next_base);
-            }
-        }
-        if (!has_next) break;
-        if (nxt != FP3_NONE) {
-            cur = nxt;
-            nxt = FP3_NONE;
-        }
-        tile = next;
-        tile_base = next_base;
-    }
-}
+// (k_fused_pass3 -- one CTA per SM, two 256-thread groups over three tile buffers -- was measured in round 1:
+// QuantumVolume 30 q -7 %, EfficientSU2 28 q +6 %; removed in round 2, the A/B is profiles/r1k_stagger_ab.txt and
+// DESIGN.md section 3.)

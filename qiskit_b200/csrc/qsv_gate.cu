@@ -2342,7 +2342,7 @@ static void build_fp_remote(const FpPass& P, const QsvPendingSwap& W, FpRemote& 
 
 // a fused pass can carry the pending swap when it reads its own buffer in the plain way
 static bool fused_swap_capable(const qsv_state* s, const FpPass& P) {
-    return s->pending_swap && !s->read_from && !s->prod_pending && !P.store_prob && !s->use_fused3;
+    return s->pending_swap && !s->read_from && !s->prod_pending && !P.store_prob;
 }
 
 static int launch_fused_swap_pass(qsv_state* s, const FpPass& P) {
@@ -2405,7 +2405,7 @@ static int launch_fused_pass(qsv_state* s, const FusedBuilt& fb, bool is_last) {
     if (trace) QSV_CUDA(cudaEventRecord(s->tev0, s->stream));
     const double2* src = s->read_from ? s->read_from : s->amp;
     s->read_from = nullptr;  // only the first pass after the request reads the other buffer
-    if (s->prod_pending && (s->use_fused3 || !s->use_product_fold)) QSV_TRY(qsv_flush_product(s));
+    if (s->prod_pending && !s->use_product_fold) QSV_TRY(qsv_flush_product(s));
     if (s->prod_pending) {
         // first pass after the product-state prologue: nothing is read, phase 0 builds its registers
         // from the per-qubit vectors (FpPass.gen_*)
@@ -2442,18 +2442,7 @@ static int launch_fused_pass(qsv_state* s, const FusedBuilt& fb, bool is_last) {
         s->ctr.write_passes++;  // one sweep written, none read
         return QSV_OK;
     }
-    if (s->use_fused3) {
-        static bool attr3_set = false;
-        const size_t tabs_max = FP_MAX_TABS * FP_NT * sizeof(uint16_t);
-        if (!attr3_set) {
-            QSV_CUDA(cudaFuncSetAttribute(k_fused_pass3, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          (int)(3 * FP_TILE * sizeof(double2) + tabs_max + 64)));
-            attr3_set = true;
-        }
-        const size_t smem3 = 3 * FP_TILE * sizeof(double2) + (size_t)P.ntabs * FP_NT * sizeof(uint16_t) + 64;
-        unsigned grid = (unsigned)std::min<uint64_t>((P.ntiles + 1) / 2, (uint64_t)s->num_sms);
-        k_fused_pass3<<<grid, FP3_NT, smem3, s->stream>>>(s->amp, src, P);
-    } else {
+    {
         unsigned grid = (unsigned)std::min<uint64_t>(P.ntiles, (uint64_t)s->num_sms * 2);
         k_fused_pass<<<grid, FP_NT, smem, s->stream>>>(s->amp, src, P);
     }
@@ -2638,7 +2627,7 @@ int qsv_apply_hgates(qsv_state* s, std::vector<HGate>& gates, int flags) {
                 s->ctr.state_passes++;
                 s->read_from = nullptr;
             }
-            if (want_prob && end == gates.size() && !passes.empty() && kind.back() == 3 && !s->use_fused3) {
+            if (want_prob && end == gates.size() && !passes.empty() && kind.back() == 3) {
                 FpPass& last = fparams.back().P;
                 if (last.nphases > 0 && last.phases[last.nphases - 1].direct) {
                     last.store_prob = 1;

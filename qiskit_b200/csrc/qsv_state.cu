@@ -99,7 +99,6 @@ void qsv_state_defaults(qsv_state* s) {
     s->use_cluster = env_int("QSV_USE_CLUSTER", 1);
     s->use_fused = env_int("QSV_USE_FUSED", 1);
     s->use_direct_store = env_int("QSV_DIRECT_STORE", 1);
-    s->use_fused3 = env_int("QSV_FUSED3", 0);
     s->use_linear_perm = env_int("QSV_LINEAR_PERM", 1);
     s->use_diag_split = env_int("QSV_DIAG_SPLIT", 1);
     s->lazy_init = env_int("QSV_LAZY_INIT", 1);
@@ -219,7 +218,6 @@ extern "C" int qsv_clone(const qsv_state* s, qsv_state** out) {
     c->use_fused = s->use_fused;
     c->use_direct_store = s->use_direct_store;
     c->use_warp_local = s->use_warp_local;
-    c->use_fused3 = s->use_fused3;
     c->use_linear_perm = s->use_linear_perm;
     c->use_diag_split = s->use_diag_split;
     c->lazy_init = s->lazy_init;
@@ -403,8 +401,6 @@ extern "C" int qsv_set_option(qsv_state* s, const char* name, int64_t value) {
         s->use_direct_store = value != 0;
     } else if (!strcmp(name, "warp_local")) {
         s->use_warp_local = value != 0;
-    } else if (!strcmp(name, "fused3")) {
-        s->use_fused3 = value != 0;
     } else if (!strcmp(name, "linear_perm")) {
         s->use_linear_perm = value != 0;
     } else if (!strcmp(name, "diag_split")) {

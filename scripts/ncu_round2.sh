@@ -11,4 +11,12 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_fu
   -o $O/qv30_fused -f python scripts/profile_run.py qv > $O/ncu_qv.log 2>&1; echo "ncu qv exit $?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_expval -s 3 -c 3 \
   -o $O/su2_expval -f python scripts/profile_run.py su2 > $O/ncu_expval.log 2>&1; echo "ncu expval exit $?"
+# gpurun brings back at most 64 MiB: summarise on the box, keep the raw metric tables, drop the reports
+for r in su2_fused qv30_fused su2_expval; do
+  if [ -f $O/$r.ncu-rep ]; then
+    python scripts/ncu_summary.py $O/$r.ncu-rep > $O/$r.summary.txt 2>&1
+    ncu -i $O/$r.ncu-rep --page raw --csv > $O/$r.raw.csv 2>/dev/null
+    rm -f $O/$r.ncu-rep
+  fi
+done
 ls -la $O
