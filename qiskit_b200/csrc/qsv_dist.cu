@@ -894,13 +894,22 @@ int qsv_dist_localize(qsv_state* s, uint64_t want_local, uint64_t keep) {
     sw.kind = 1;
     sw.k = 0;
     std::vector<int> victims;
+    // preferred victims sit at or above min_lpos (long contiguous runs); the low positions are taken
+    // only when a term's X / Y factors leave nothing else
     for (int q = s->n - 1; q >= 0; --q)
-        if (s->perm[q] < s->n_local && s->perm[q] >= d->min_lpos && !((keep >> q) & 1ull)) victims.push_back(q);
-    std::sort(victims.begin(), victims.end(), [&](int a, int b) { return s->perm[a] > s->perm[b]; });
+        if (s->perm[q] < s->n_local && !((keep >> q) & 1ull)) victims.push_back(q);
+    std::sort(victims.begin(), victims.end(), [&](int a, int b) {
+        const bool ha = s->perm[a] >= d->min_lpos, hb = s->perm[b] >= d->min_lpos;
+        if (ha != hb) return ha;
+        return s->perm[a] > s->perm[b];
+    });
     size_t vi = 0;
     for (int q = 0; q < s->n; ++q) {
         if (!((want_local >> q) & 1ull) || s->perm[q] < s->n_local) continue;
-        if (vi >= victims.size()) QSV_FAIL(QSV_ERR_UNSUPPORTED, "sharded state: no local qubit left to evict");
+        if (vi >= victims.size())
+            QSV_FAIL(QSV_ERR_UNSUPPORTED,
+                     "sharded state: a Pauli term has X / Y factors on more qubits than a slab holds (%d local qubits)",
+                     s->n_local);
         sw.gin[sw.k] = q;
         sw.lout[sw.k] = victims[vi++];
         ++sw.k;

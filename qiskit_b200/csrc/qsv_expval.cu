@@ -642,7 +642,7 @@ extern "C" int qsv_expval_pauli_batch(const qsv_state* cs, uint64_t n_terms, con
             auto evictable = [&](uint64_t kp) {
                 int c = 0;
                 for (int q = 0; q < s->n; ++q)
-                    if (s->perm[q] < s->n_local && s->perm[q] >= qsv_dist_min_lpos(s) && !((kp >> q) & 1ull)) ++c;
+                    if (s->perm[q] < s->n_local && !((kp >> q) & 1ull)) ++c;
                 return c;
             };
             for (size_t t : remaining) {
