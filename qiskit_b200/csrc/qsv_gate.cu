@@ -2245,8 +2245,14 @@ static void trace_fused_pass(const FpPass& P, FILE* f) {
                 P.phases[p].rcoef != FP_NOCOEF ? "r" : "", P.phases[p].wcoef != FP_NOCOEF ? "w" : "");
         for (int i = 0; i < P.phases[p].nsub; ++i) cnt[P.subs[P.phases[p].sub_first + i].kind]++;
     }
-    fprintf(f, " | d1c %d d1r %d d1l %d d1ry %d d1h %d d2c %d d2r %d diag %d diagb %d diagu %d | tabs %d\n", cnt[0], cnt[1],
-            cnt[6], cnt[7], cnt[8] + cnt[9], cnt[2], cnt[3], cnt[4], cnt[10], cnt[5], P.ntabs);
+    int same = 0;
+    for (int p = 0; p < P.nphases; ++p)
+        for (int i = 0; i < P.phases[p].nsub; ++i) {
+            const FpSub& sb = P.subs[P.phases[p].sub_first + i];
+            if (sb.kind == FP_DIAG && P.diags[sb.mat].all_same) ++same;
+        }
+    fprintf(f, " | d1c %d d1r %d d1l %d d1ry %d d1h %d d2c %d d2r %d diag %d (per-thread scalar %d) diagb %d diagu %d | tabs %d\n",
+            cnt[0], cnt[1], cnt[6], cnt[7], cnt[8] + cnt[9], cnt[2], cnt[3], cnt[4], same, cnt[10], cnt[5], P.ntabs);
 }
 
 static int upload_product_tables(qsv_state* s, uint64_t neutral, const std::vector<cplx>& extra);
