@@ -175,3 +175,30 @@ def partial_transpose(rho, qargs) -> np.ndarray:
     for i in n - 1 - np.array(qargs):  # qubit q is tensor axis n-1-q (:849)
         lst[i], lst[i + n] = lst[i + n], lst[i]
     return np.reshape(np.transpose(arr, lst), rho.shape)
+
+
+def evolve_superop(rho: np.ndarray, sop: np.ndarray, qargs=None) -> np.ndarray:
+    """``SuperOp._evolve`` (qiskit/quantum_info/operators/channel/superop.py:234-292) for qubit channels:
+    full system = superoperator times the column-stacked (Fortran-order) density matrix; a subsystem =
+    the reference's einsum contraction over the row and column tensor axes of ``qargs``."""
+    n = int(round(np.log2(rho.shape[0])))
+    if qargs is None:
+        vec = np.ravel(rho, order="F")
+        return np.reshape(np.dot(sop, vec), rho.shape, order="F")
+    k = len(qargs)
+    tensor = np.reshape(rho, (2,) * (2 * n))
+    mat = np.reshape(sop, (2,) * (4 * k))
+    indices = [n - 1 - q for q in qargs] + [2 * n - 1 - q for q in qargs]
+    rank = tensor.ndim
+    indices_tensor = list(range(rank))
+    for j, index in enumerate(indices):
+        indices_tensor[index] = rank + j
+    mat_contract = list(reversed(range(rank, rank + len(indices))))
+    mat_free = list(reversed(indices))
+    out = np.einsum(tensor, indices_tensor, mat, mat_free + mat_contract)
+    return np.reshape(out, rho.shape)
+
+
+def kraus_to_superop(kraus) -> np.ndarray:
+    """``_kraus_to_superop`` (operators/channel/transformations.py): sum_i conj(K_i) (x) K_i."""
+    return sum(np.kron(np.conj(np.asarray(k, dtype=complex)), np.asarray(k, dtype=complex)) for k in kraus)

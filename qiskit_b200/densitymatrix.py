@@ -350,9 +350,30 @@ class DensityMatrix:
         if _is_instruction(other):
             ret._evolve_instruction_inplace(other, qargs)
             return ret
+        from .channels import as_superop_matrix
+
+        sop = as_superop_matrix(other)        # QuantumChannel branch (densitymatrix.py:329-336)
+        if sop is not None:
+            ret._evolve_superop_inplace(sop, qargs)
+            return ret
         mat = np.asarray(getattr(other, "data", other), dtype=np.complex128)
         ret._evolve_operator_inplace(mat, qargs)
         return ret
+
+    def _evolve_superop_inplace(self, sop, qargs=None):
+        """``SuperOp._evolve`` (operators/channel/superop.py:234-292) on the device: the superoperator acts on
+        the column-stacked density matrix (row bits low, column bits high), i.e. it is one dense 2k-qubit
+        matrix on the handle qubits ``[q + n for q in qargs] + qargs`` (rows live on qubits q + n)."""
+        qa = self._qargs(qargs)
+        k = len(qa)
+        sop = np.asarray(sop, dtype=np.complex128)
+        if sop.shape != (1 << (2 * k), 1 << (2 * k)):
+            raise QiskitError("Operator input dimensions are not equal to statevector subsystem dimensions.")
+        if 2 * k > _lib.MAX_GATE_QUBITS:
+            raise QiskitError(f"a SuperOp on {k} qubits exceeds the engine limit of {_lib.MAX_GATE_QUBITS // 2}")
+        stream = GateStream()
+        stream.matrix(sop, [q + self._n for q in qa] + qa)
+        self._flush(stream)
 
     def _evolve_operator_inplace(self, mat, qargs=None):
         """Device counterpart of ``_evolve_operator`` (densitymatrix.py:720-750)."""

@@ -130,3 +130,35 @@ def test_reverse_and_partial_transpose():
     # partial transpose of a product state transposes that factor
     np.testing.assert_allclose(dref.partial_transpose(rho, [2]), np.kron(a.T, b), atol=1e-14)
     np.testing.assert_allclose(dref.partial_transpose(rho, [0, 1]), np.kron(a, b.T), atol=1e-14)
+
+
+# ---- channels: SuperOp._evolve (operators/channel/superop.py:234-292) --------------------------------
+
+def test_superop_evolve_reference_goldens():
+    """test_superop.py:112-129: identity, Hadamard and completely depolarizing channel on |1><1|."""
+    rho = np.array([[0, 0], [0, 1]], dtype=complex)
+    np.testing.assert_allclose(dref.evolve_superop(rho, np.eye(4)), rho, atol=1e-15)
+    h = np.array([[1, 1], [1, -1]]) / np.sqrt(2)
+    np.testing.assert_allclose(dref.evolve_superop(rho, np.kron(h.conj(), h)), np.array([[1, -1], [-1, 1]]) / 2, atol=1e-15)
+    depol1 = np.array([[1, 0, 0, 1], [0, 0, 0, 0], [0, 0, 0, 0], [1, 0, 0, 1]]) / 2      # channel_test_case.py:68-72, p = 1
+    np.testing.assert_allclose(dref.evolve_superop(rho, depol1), np.eye(2) / 2, atol=1e-15)
+
+
+@pytest.mark.parametrize("qargs", [[0], [1], [2], [0, 2], [2, 0], [0, 1, 2], [2, 1, 0]])
+def test_superop_evolve_subsystem_equals_embedded_kraus(qargs):
+    """test_superop.py:131-190 checks subsystems against tensored superoperators; here the same property
+    through Kraus operators: evolving `qargs` = sum_i (K_i on qargs) rho (K_i on qargs)^dagger."""
+    rng = np.random.default_rng(len(qargs) * 7 + qargs[0])
+    rho = random_density(3, 5)
+    k = len(qargs)
+    kraus = [rng.standard_normal((1 << k, 1 << k)) + 1j * rng.standard_normal((1 << k, 1 << k)) for _ in range(3)]
+    got = dref.evolve_superop(rho, dref.kraus_to_superop(kraus), qargs)
+    want = np.zeros_like(rho)
+    for op in kraus:
+        cols = [ref.evolve_operator(rho[:, c].copy(), op, qargs) for c in range(rho.shape[1])]     # K rho
+        left = np.stack(cols, axis=1)
+        rows = [ref.evolve_operator(left[r, :].conj().copy(), op, qargs).conj() for r in range(rho.shape[0])]  # (K rho) K^dagger
+        want += np.stack(rows, axis=0)
+    np.testing.assert_allclose(got, want, atol=1e-12)
+    if qargs == [0, 1, 2]:
+        np.testing.assert_allclose(dref.evolve_superop(rho, dref.kraus_to_superop(kraus)), want, atol=1e-12)

@@ -251,3 +251,42 @@ def test_density_reset_and_measure_on_all_twelve_qubits():
     idx = int(outcome, 2)
     d = post.data
     assert abs(d[idx, idx] - 1.0) < 1e-9 and np.count_nonzero(np.abs(d) > 1e-9) == 1
+
+
+@pytest.mark.parametrize("n,qargs", [(1, None), (3, [0]), (3, [2]), (3, [0, 2]), (3, [2, 0]), (3, [2, 1, 0]), (6, [4, 1]),
+                                     (7, [5, 0, 3]), (7, None)])
+def test_evolve_by_a_channel(n, qargs):
+    """DensityMatrix.evolve(QuantumChannel) (densitymatrix.py:329-336 -> SuperOp._evolve): the superoperator
+    as one dense 2k-qubit matrix on the handle, against the oracle's restatement (pinned to
+    test_superop.py:112-129 in tests/test_density_oracle.py)."""
+    from qiskit_b200.channels import SuperOp
+
+    rng = np.random.default_rng(n * 11 + (len(qargs) if qargs else 0))
+    k = n if qargs is None else len(qargs)
+    if k > 6:
+        with pytest.raises(QiskitError):
+            DensityMatrix(random_density(n, 3)).evolve(SuperOp(np.eye(1 << (2 * k))), qargs)
+        return
+    rho = random_density(n, 3)
+    kraus = [rng.standard_normal((1 << k, 1 << k)) + 1j * rng.standard_normal((1 << k, 1 << k)) for _ in range(2)]
+    chan = SuperOp.from_kraus(kraus)
+    np.testing.assert_allclose(chan.data, dref.kraus_to_superop(kraus), atol=0)
+    dm = DensityMatrix(rho)
+    got = dm.evolve(chan, qargs).data
+    np.testing.assert_allclose(got, dref.evolve_superop(rho, chan.data, qargs), atol=TOL * max(1.0, np.abs(got).max()))
+    np.testing.assert_array_equal(dm.data, rho)                      # evolve never mutates
+    dense = rng.standard_normal((1 << (2 * k),) * 2) + 1j * rng.standard_normal((1 << (2 * k),) * 2)   # non-CP map
+    got = dm.evolve(SuperOp(dense), qargs).data
+    np.testing.assert_allclose(got, dref.evolve_superop(rho, dense, qargs), atol=TOL * max(1.0, np.abs(got).max()))
+
+
+def test_channel_goldens_on_device():
+    """test_superop.py:112-129 on the device."""
+    from qiskit_b200.channels import SuperOp
+
+    rho = DensityMatrix(np.array([[0, 0], [0, 1]], dtype=complex))
+    h = np.array([[1, 1], [1, -1]]) / np.sqrt(2)
+    np.testing.assert_allclose(rho.evolve(SuperOp(np.eye(4))).data, [[0, 0], [0, 1]], atol=TOL)
+    np.testing.assert_allclose(rho.evolve(SuperOp(np.kron(h.conj(), h))).data, np.array([[1, -1], [-1, 1]]) / 2, atol=TOL)
+    depol1 = np.array([[1, 0, 0, 1], [0, 0, 0, 0], [0, 0, 0, 0], [1, 0, 0, 1]]) / 2
+    np.testing.assert_allclose(rho.evolve(SuperOp(depol1)).data, np.eye(2) / 2, atol=TOL)
