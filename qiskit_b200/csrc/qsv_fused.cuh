@@ -70,11 +70,6 @@ struct FpPass {
     int32_t nphases;
     int32_t ntabs;
     int32_t warp_local;    // phases exchange data inside warps only (__syncwarp between phases)
-    // Small states (a CTA sees one or two tiles): the first touch of every 64-byte line of this descriptor
-    // misses the constant cache, one miss after the other on the dependent path of the arithmetic
-    // (measured: ~40 us per pass at 20 qubits for ~5 us of data movement).  warm > 0: the warps touch the
-    // used lines with independent loads while the first tile is in flight.
-    int32_t warm, used_subs, used_mats, used_diags;
     // gen_h > 0: product-state prologue folded into this (first) pass.  No tile is read: the state
     // is a product over qubits, so every tile is the same 2^12 amplitudes (the product over the tile's
     // qubits, gen_tile, in tile-index order) times one scalar,
@@ -604,18 +599,6 @@ __device__ __forceinline__ void fp_pass_body(double2* amp, const double2* src, c
     if (tile >= P.ntiles) return;
     uint64_t tile_base = tile_base_of(tile);
     issue_load(tile_base);
-    if (P.warm) {
-        const int w = (int)(t >> 5);
-        double acc = 0.0;
-        for (int i = w * 8; i < P.used_mats; i += 8 * (FP_NT / 32)) acc += P.mats[i];
-        const double* ph = reinterpret_cast<const double*>(P.phases);
-        for (int i = w * 8; i < P.nphases * (int)(sizeof(FpPhase) / 8); i += 8 * (FP_NT / 32)) acc += ph[i];
-        const double* sb = reinterpret_cast<const double*>(P.subs);
-        for (int i = w * 8; i < P.used_subs; i += 8 * (FP_NT / 32)) acc += sb[i];
-        const double* dg = reinterpret_cast<const double*>(P.diags);
-        for (int i = w * 8; i < P.used_diags * (int)(sizeof(FpDiag) / 8); i += 8 * (FP_NT / 32)) acc += dg[i];
-        if (acc == 1.2345678e-301) tabs_sm[0] = 0;  // never true: keeps the loads
-    }
     while (true) {
         asm volatile("cp.async.wait_group 0;\n" ::: "memory");
         __syncthreads();  // tile (and, first time, the tables) visible to every thread

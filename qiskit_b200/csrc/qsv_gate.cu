@@ -2219,11 +2219,6 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
     P.nphases = (int)sels.size();
     P.ntabs = (int)(tabs.size() / FP_NT);
     P.ntiles = (uint32_t)(1ull << (n - FP_T));
-    static const bool warm_ok = !(getenv("QSV_NO_WARM") && atoi(getenv("QSV_NO_WARM")));
-    P.warm = warm_ok && P.ntiles <= 4u * 2u * 148u;  // at most ~4 tiles per CTA: the descriptor's cold start matters
-    P.used_subs = nsubs;
-    P.used_mats = nmat;
-    P.used_diags = (int)diags.size();
     P.index_base = s->world > 1 ? ((uint64_t)s->rank << s->n_local) : 0;
     const size_t tabs_bytes = tabs.size() * sizeof(uint16_t);
     const size_t diag_bytes = diags.size() * sizeof(FpDiag);
