@@ -818,7 +818,7 @@ def cpu_baseline(args, repeats: int = 3, warm: bool = True) -> dict:
             "spread_s": {k: [round(v, 4) for v in vs] for k, vs in spread.items()}}
 
 
-def model_check(qubits: int = 20) -> dict:
+def model_check(qubits: int = 24) -> dict:
     """Does the per-op model behind the extrapolation reproduce a FULLY executed evaluation?  One
     complete EfficientSU2 reps=4 + Heisenberg evaluation at `qubits` on the oracle, against the same
     model (per-op medians at that width x op counts)."""
@@ -848,7 +848,11 @@ def model_check(qubits: int = 20) -> dict:
     t_model = (2 * n * 5 * model["per_gate_1q_s"] + (n - 1) * 4 * model["per_gate_2q_s"]
                + n_terms * model["per_term_s"])
     return {"qubits": n, "full_eval_s": t_gates + t_terms, "full_gates_s": t_gates, "full_terms_s": t_terms,
-            "model_s": t_model, "model_over_measured": t_model / (t_gates + t_terms), "terms": n_terms}
+            "model_s": t_model, "model_over_measured": t_model / (t_gates + t_terms), "terms": n_terms,
+            "model_per_gate_1q_s": model["per_gate_1q_s"], "model_per_gate_2q_s": model["per_gate_2q_s"],
+            "model_per_term_s": model["per_term_s"],
+            "note": "at 24 q an operation takes ~0.1 s, like the 28 q sample it stands for; at 20 q (ms per "
+                    "operation) allocation and thread start-up dominate and the same check is meaningless"}
 
 
 def run_reference(args, dist: Dist) -> dict | None:
@@ -856,7 +860,7 @@ def run_reference(args, dist: Dist) -> dict | None:
     installable here -- Rust).  Each STEP is a bounded sample of configs[1] (see cpu_baseline);
     `ms_per_step` is the time the sample really took, `value` the evals/s it extrapolates to.
     configs[0] is executed in full once (`config0`), and the extrapolation model is checked
-    against a fully executed 20-qubit evaluation (`model_check`)."""
+    against a fully executed 24-qubit evaluation (`model_check`)."""
     if dist.rank != 0:
         return None
     vals, step_s = [], []
@@ -894,7 +898,7 @@ def run_reference(args, dist: Dist) -> dict | None:
         "gpu_launches": 0,
     }
     try:
-        res["model_check"] = model_check(20)
+        res["model_check"] = model_check(24)
     except Exception as exc:  # noqa: BLE001
         res["model_check"] = {"error": repr(exc)}
     return res
