@@ -32,11 +32,13 @@ if "reference" in sys.argv:
     # every host core (must be set before NumPy / OpenBLAS / libgomp are loaded)
     for _v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
         os.environ[_v] = str(os.cpu_count() or 1)
-if int(os.environ.get("WORLD_SIZE", "1")) > 1:
-    # the engine's own NCCL communicator reports its rank lines (stderr keeps stdout = one JSON line)
-    os.environ.setdefault("NCCL_DEBUG", "INFO")
-    os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+if int(os.environ.get("WORLD_SIZE", "1")) > 1 and os.environ.get("RANK", "0") == "0":
+    # The engine's own NCCL communicator reports its version and "rank R nranks N" lines where NCCL's log
+    # already goes (the box presets NCCL_DEBUG=VERSION; stdout by default): rank 0 only, INIT subsystem only,
+    # and always BEFORE the JSON line, which stays the last line of stdout.
+    if os.environ.get("NCCL_DEBUG", "").upper() not in ("INFO", "TRACE"):
+        os.environ["NCCL_DEBUG"] = "INFO"
+        os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
 
 import argparse
 import ctypes as C
