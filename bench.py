@@ -32,13 +32,15 @@ if "reference" in sys.argv:
     # every host core (must be set before NumPy / OpenBLAS / libgomp are loaded)
     for _v in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
         os.environ[_v] = str(os.cpu_count() or 1)
+_NCCL_LOG = None
 if int(os.environ.get("WORLD_SIZE", "1")) > 1 and os.environ.get("RANK", "0") == "0":
-    # The engine's own NCCL communicator reports its version and "rank R nranks N" lines where NCCL's log
-    # already goes (the box presets NCCL_DEBUG=VERSION; stdout by default): rank 0 only, INIT subsystem only,
-    # and always BEFORE the JSON line, which stays the last line of stdout.
-    if os.environ.get("NCCL_DEBUG", "").upper() not in ("INFO", "TRACE"):
-        os.environ["NCCL_DEBUG"] = "INFO"
-        os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
+    # The engine's own NCCL communicators log their version and "rank R nranks N" lines (rank 0, INIT subsystem)
+    # into a file; main() replays those few lines to stdout and stderr BEFORE the JSON line, which stays the
+    # last line of stdout (NCCL itself still writes at process exit).
+    _NCCL_LOG = f"/tmp/qsv_nccl_rank0_{os.getpid()}.log"
+    os.environ["NCCL_DEBUG"] = "INFO"
+    os.environ["NCCL_DEBUG_SUBSYS"] = "INIT"
+    os.environ["NCCL_DEBUG_FILE"] = _NCCL_LOG
 
 import argparse
 import ctypes as C
@@ -912,6 +914,12 @@ def main():
     try:
         res = run_reference(args, dist) if args.impl == "reference" else run_ours(args, dist)
         if dist.rank == 0 and res is not None:
+            if _NCCL_LOG and os.path.exists(_NCCL_LOG):
+                keep = [ln.rstrip() for ln in open(_NCCL_LOG, errors="replace")
+                        if "NCCL version" in ln or ("nranks" in ln and "Init COMPLETE" in ln)]
+                for ln in keep[:12]:
+                    print(ln, file=sys.stderr)
+                    print(ln)
             print(json.dumps(res), flush=True)
     finally:
         dist.close()
