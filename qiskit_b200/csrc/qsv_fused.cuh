@@ -32,7 +32,7 @@
 #define FP_NOCOEF 0xffffffffu
 
 enum { FP_D1C = 0, FP_D1R = 1, FP_D2C = 2, FP_D2R = 3, FP_DIAG = 4, FP_DIAGU = 5, FP_D1L = 6, FP_D1RY = 7, FP_D1H = 8, FP_D1HY = 9,
-       FP_DIAGB = 10 };
+       FP_DIAGB = 10, FP_D1L4 = 11, FP_D1H4 = 12, FP_D2C2 = 13, FP_D1R4 = 14 };
 
 struct FpPhase {           // 80 bytes
     uint16_t rd[16];       // register r is read from byte offset (thread offset ^ rd[r]) of the tile buffer
@@ -468,6 +468,31 @@ __device__ __forceinline__ void fp_apply(double2 (&v)[16], const FpPass& P, int 
         case FP_D1L * 16 + 1: fp_d1l<1>(v, P, mo); break;
         case FP_D1L * 16 + 2: fp_d1l<2>(v, P, mo); break;
         case FP_D1L * 16 + 3: fp_d1l<3>(v, P, mo); break;
+        case FP_D1L4 * 16:  // four lifted rotations, one per register bit, behind ONE dispatch: a rotation is only
+                            // 48 DFMA per thread, and every dispatch costs a dependent descriptor -> branch -> constants chain
+            fp_d1l<0>(v, P, mo);
+            fp_d1l<1>(v, P, mo + 2);
+            fp_d1l<2>(v, P, mo + 4);
+            fp_d1l<3>(v, P, mo + 6);
+            break;
+        case FP_D1H4 * 16:  // unnormalised Hadamard butterflies on all four register bits (X-basis change of a phase)
+            fp_d1h<0, false>(v);
+            fp_d1h<1, false>(v);
+            fp_d1h<2, false>(v);
+            fp_d1h<3, false>(v);
+            break;
+        case FP_D1H4 * 16 + 1:  // ... the Y-basis change
+            fp_d1h<0, true>(v);
+            fp_d1h<1, true>(v);
+            fp_d1h<2, true>(v);
+            fp_d1h<3, true>(v);
+            break;
+        case FP_D1R4 * 16:  // four real 2x2 gates, one per register bit
+            fp_d1r<0>(v, P, mo);
+            fp_d1r<1>(v, P, mo + 4);
+            fp_d1r<2>(v, P, mo + 8);
+            fp_d1r<3>(v, P, mo + 12);
+            break;
         case FP_D2C * 16 + 4: fp_d2c<0, 1>(v, P, mo); break;
         case FP_D2C * 16 + 8: fp_d2c<0, 2>(v, P, mo); break;
         case FP_D2C * 16 + 12: fp_d2c<0, 3>(v, P, mo); break;

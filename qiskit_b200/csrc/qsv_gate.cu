@@ -1611,6 +1611,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
     for (int b = 0; b < n && popc64(active) < FP_T; ++b) active |= 1ull << b;  // low bits first
     if (popc64(active) != FP_T) return QSV_OK;
     static const bool use_lifting = !getenv("QSV_NO_LIFT");
+    static const bool use_d1l4 = !(getenv("QSV_NO_D1L4") && atoi(getenv("QSV_NO_D1L4")));
     static const bool use_bilinear = getenv("QSV_BILINEAR") && atoi(getenv("QSV_BILINEAR"));  // measured slower (profiles/r2_bilinear_tables_ab.txt): opt-in
     FpPass& P = out.P;
     memset(&P, 0, sizeof P);
@@ -2181,6 +2182,84 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
             ++nsubs;
             ++cnt;
         }
+        // peephole: four consecutive lifted rotations on the four different register bits (they commute)
+        // become one FP_D1L4 sub-op -- the RY layer of a hardware-efficient ansatz, every phase of it
+        if (use_d1l4) {
+            const int first = ph.sub_first;
+            for (int i = first; i + 3 < nsubs; ++i) {
+                int seen = 0;
+                bool ok4 = true;
+                for (int j = 0; j < 4 && ok4; ++j) {
+                    const FpSub& q = P.subs[i + j];
+                    ok4 = q.kind == FP_D1L && !((seen >> q.b) & 1);
+                    seen |= 1 << q.b;
+                }
+                if (!ok4 || seen != 15) {
+                    // the same for four butterflies of one kind (basis change of an X / Y family)
+                    const int k0 = P.subs[i].kind;
+                    seen = 0;
+                    bool okh = k0 == FP_D1H || k0 == FP_D1HY;
+                    for (int j = 0; j < 4 && okh; ++j) {
+                        const FpSub& q = P.subs[i + j];
+                        okh = q.kind == k0 && !((seen >> q.b) & 1);
+                        seen |= 1 << q.b;
+                    }
+                    if (!okh || seen != 15) continue;
+                    FpSub m;
+                    memset(&m, 0, sizeof m);
+                    m.kind = FP_D1H4;
+                    m.b = k0 == FP_D1HY ? 1 : 0;
+                    P.subs[i] = m;
+                    for (int j = i + 4; j < nsubs; ++j) P.subs[j - 3] = P.subs[j];
+                    nsubs -= 3;
+                    cnt -= 3;
+                    continue;
+                }
+                if (nmat + 8 > FP_MAX_MAT) continue;
+                double c8[8];
+                for (int j = 0; j < 4; ++j) {
+                    const FpSub& q = P.subs[i + j];
+                    c8[2 * q.b] = P.mats[q.mat];
+                    c8[2 * q.b + 1] = P.mats[q.mat + 1];
+                }
+                FpSub m;
+                memset(&m, 0, sizeof m);
+                m.kind = FP_D1L4;
+                m.mat = (uint16_t)nmat;
+                for (int j = 0; j < 8; ++j) P.mats[nmat++] = c8[j];
+                P.subs[i] = m;
+                for (int j = i + 4; j < nsubs; ++j) P.subs[j - 3] = P.subs[j];
+                nsubs -= 3;
+                cnt -= 3;
+            }
+        }
+        if (use_d1l4) {
+            // ... four real 2x2 gates on the four register bits (Hadamard / RY layers that are not lifted)
+            for (int i = ph.sub_first; i + 3 < nsubs; ++i) {
+                int seen = 0;
+                bool ok4 = nmat + 16 <= FP_MAX_MAT;
+                for (int j = 0; j < 4 && ok4; ++j) {
+                    const FpSub& q = P.subs[i + j];
+                    ok4 = q.kind == FP_D1R && !((seen >> q.b) & 1);
+                    seen |= 1 << q.b;
+                }
+                if (!ok4 || seen != 15) continue;
+                double c16[16];
+                for (int j = 0; j < 4; ++j) {
+                    const FpSub& q = P.subs[i + j];
+                    for (int e = 0; e < 4; ++e) c16[4 * q.b + e] = P.mats[q.mat + e];
+                }
+                FpSub m;
+                memset(&m, 0, sizeof m);
+                m.kind = FP_D1R4;
+                m.mat = (uint16_t)nmat;
+                for (int j = 0; j < 16; ++j) P.mats[nmat++] = c16[j];
+                P.subs[i] = m;
+                for (int j = i + 4; j < nsubs; ++j) P.subs[j - 3] = P.subs[j];
+                nsubs -= 3;
+                cnt -= 3;
+            }
+        }
         ph.nsub = (uint8_t)cnt;
         for (size_t i = 0; i < ps.sel.size(); ++i)
             if (ps.role[i] == 4) absorb(ops[ps.sel[i]]);  // the data stays put; later readers use the new map
@@ -2236,7 +2315,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
 }
 
 static void trace_fused_pass(const FpPass& P, FILE* f) {
-    int cnt[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    int cnt[15] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     fprintf(f, "[fused] T bits:");
     for (int b = 0; b < FP_T; ++b) fprintf(f, " %d", P.pos[b]);
     fprintf(f, " | %sphases %d:", P.warp_local ? "warp-local " : "", P.nphases);
@@ -2251,8 +2330,8 @@ static void trace_fused_pass(const FpPass& P, FILE* f) {
             const FpSub& sb = P.subs[P.phases[p].sub_first + i];
             if (sb.kind == FP_DIAG && P.diags[sb.mat].all_same) ++same;
         }
-    fprintf(f, " | d1c %d d1r %d d1l %d d1ry %d d1h %d d2c %d d2r %d diag %d (per-thread scalar %d) diagb %d diagu %d | tabs %d\n",
-            cnt[0], cnt[1], cnt[6], cnt[7], cnt[8] + cnt[9], cnt[2], cnt[3], cnt[4], same, cnt[10], cnt[5], P.ntabs);
+    fprintf(f, " | d1c %d d1r %d d1l %d (+%d x4) d1ry %d d1h %d d2c %d d2r %d diag %d (per-thread scalar %d) diagb %d diagu %d | tabs %d\n",
+            cnt[0], cnt[1] + 4 * cnt[14], cnt[6], cnt[11], cnt[7], cnt[8] + cnt[9] + 4 * cnt[12], cnt[2] + 2 * cnt[13], cnt[3], cnt[4], same, cnt[10], cnt[5], P.ntabs);
 }
 
 static int upload_product_tables(qsv_state* s, uint64_t neutral, const std::vector<cplx>& extra);
