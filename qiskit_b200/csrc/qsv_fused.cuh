@@ -32,7 +32,7 @@
 #define FP_NOCOEF 0xffffffffu
 
 enum { FP_D1C = 0, FP_D1R = 1, FP_D2C = 2, FP_D2R = 3, FP_DIAG = 4, FP_DIAGU = 5, FP_D1L = 6, FP_D1RY = 7, FP_D1H = 8, FP_D1HY = 9,
-       FP_DIAGB = 10, FP_D1L4 = 11, FP_D1H4 = 12, FP_D2C2 = 13, FP_D1R4 = 14 };
+       FP_DIAGB = 10, FP_D1L4 = 11, FP_D1H4 = 12, FP_D2C2 = 13, FP_D1R4 = 14, FP_DIAGUS = 15 };
 
 struct FpPhase {           // 80 bytes
     uint16_t rd[16];       // register r is read from byte offset (thread offset ^ rd[r]) of the tile buffer
@@ -508,6 +508,20 @@ __device__ __forceinline__ void fp_apply(double2 (&v)[16], const FpPass& P, int 
         case FP_DIAGU * 16: {  // register-bit factor of a separable diagonal: 16 uniform coefficients
 #pragma unroll
             for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], make_double2(P.mats[mo + 2 * r], P.mats[mo + 2 * r + 1]));
+            break;
+        }
+        case FP_DIAGUS * 16: {
+            // a separable diagonal in one dispatch: the per-thread scalar of its non-register bits (table
+            // `b2`, all_same) is requested first, the 16 uniform register-bit coefficients are applied while
+            // the look-up is in flight, then the scalar
+            const FpDiag& d = P.diags[P.subs[si].pad];
+            uint32_t glob = 0;
+            for (int j = 0; j < d.nglob; ++j) glob |= (uint32_t)((tile_base >> d.gbit[j]) & 1ull) << d.gj[j];
+            const double2 c = __ldg(P.gdata + d.table_off + (tabs_sm[d.tab * FP_NT + t] | glob));
+#pragma unroll
+            for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], make_double2(P.mats[mo + 2 * r], P.mats[mo + 2 * r + 1]));
+#pragma unroll
+            for (int r = 0; r < 16; ++r) fp_cmul_inplace(v[r], c);
             break;
         }
         case FP_DIAGB * 16: fp_diagb(v, P, mo, tabs_sm, tile_base, t); break;

@@ -2234,6 +2234,24 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
             }
         }
         if (use_d1l4) {
+            // ... a uniform register-bit diagonal next to a per-thread-scalar table (the two halves of a
+            // separable diagonal such as an RZ layer; diagonals commute, either order)
+            for (int i = ph.sub_first; i + 1 < nsubs; ++i) {
+                const FpSub a = P.subs[i], b2 = P.subs[i + 1];
+                const bool au = a.kind == FP_DIAGU, bu = b2.kind == FP_DIAGU;
+                const FpSub& u = au ? a : b2;
+                const FpSub& d = au ? b2 : a;
+                if (au == bu || d.kind != FP_DIAG || !diags[d.mat].all_same) continue;
+                FpSub m;
+                memset(&m, 0, sizeof m);
+                m.kind = FP_DIAGUS;
+                m.mat = u.mat;
+                m.pad = d.mat;
+                P.subs[i] = m;
+                for (int j = i + 2; j < nsubs; ++j) P.subs[j - 1] = P.subs[j];
+                nsubs -= 1;
+                cnt -= 1;
+            }
             // ... four real 2x2 gates on the four register bits (Hadamard / RY layers that are not lifted)
             for (int i = ph.sub_first; i + 3 < nsubs; ++i) {
                 int seen = 0;
@@ -2315,7 +2333,7 @@ static int build_fused_pass(qsv_state* s, const std::vector<HGate>& gates, const
 }
 
 static void trace_fused_pass(const FpPass& P, FILE* f) {
-    int cnt[15] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    int cnt[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     fprintf(f, "[fused] T bits:");
     for (int b = 0; b < FP_T; ++b) fprintf(f, " %d", P.pos[b]);
     fprintf(f, " | %sphases %d:", P.warp_local ? "warp-local " : "", P.nphases);
@@ -2331,7 +2349,7 @@ static void trace_fused_pass(const FpPass& P, FILE* f) {
             if (sb.kind == FP_DIAG && P.diags[sb.mat].all_same) ++same;
         }
     fprintf(f, " | d1c %d d1r %d d1l %d (+%d x4) d1ry %d d1h %d d2c %d d2r %d diag %d (per-thread scalar %d) diagb %d diagu %d | tabs %d\n",
-            cnt[0], cnt[1] + 4 * cnt[14], cnt[6], cnt[11], cnt[7], cnt[8] + cnt[9] + 4 * cnt[12], cnt[2] + 2 * cnt[13], cnt[3], cnt[4], same, cnt[10], cnt[5], P.ntabs);
+            cnt[0], cnt[1] + 4 * cnt[14], cnt[6], cnt[11], cnt[7], cnt[8] + cnt[9] + 4 * cnt[12], cnt[2] + 2 * cnt[13], cnt[3], cnt[4] + cnt[15], same, cnt[10], cnt[5] + cnt[15], P.ntabs);
 }
 
 static int upload_product_tables(qsv_state* s, uint64_t neutral, const std::vector<cplx>& extra);
