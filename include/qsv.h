@@ -123,6 +123,22 @@ int qsv_expval_pauli_batch(const qsv_state* s, uint64_t n_terms, const uint64_t*
 /* <s|s> and <a|b> = sum conj(a_i) b_i (Statevector.inner, statevector.py:399-413) */
 int qsv_norm2(const qsv_state* s, double* out);
 int qsv_inner(const qsv_state* a, const qsv_state* b, double* out_c128);
+/* <a|b> like qsv_inner, for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid allocation).  NO COUNTERPART IN THE REFERENCE.
+ * The call allocates nothing (no cudaMalloc / cudaFree / pinned host memory / pooled handle):
+ * the per-block partial sums live in one file-scope `static __device__ __align__(256)` array of 16640 bytes
+ * (1024 block partials x {re, im} + one 256-byte line for the arrival ticket) that every GPU loading the
+ * library holds until the process exits (csrc/qsv_noalloc.cu; its device address is looked up once per
+ * device with cudaGetSymbolAddress).
+ *   a_c128, b_c128: DEVICE pointers, `count` interleaved complex128 each, 16-byte aligned, on `device`;
+ *   out_c128: DEVICE pointer to 2 doubles (re, im); stream: a cudaStream_t of `device` (NULL = default).
+ *   Asynchronous: the result is valid once the work queued on `stream` has completed.
+ * Limit: count <= 2^30 amplitudes (16 GiB per operand); larger counts return QSV_ERR_INVALID with a
+ * message naming the limit -- use qsv_inner there.  Every call shares the one array: calls that overlap on
+ * the GPU (different streams, two host threads on one device) race on it and must be serialised by the
+ * caller; calls on one stream are safe back to back.  Makes `device` the calling thread's current device. */
+int qsv_inner_static_scratch(int device, const double* a_c128, const double* b_c128, uint64_t count,
+                             double* out_c128, void* stream);
 
 /* ---- probabilities and sampling ---------------------------------------- */
 /* Statevector.probabilities (statevector.py:663-668) + _subsystem_probabilities

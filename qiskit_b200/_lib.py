@@ -76,6 +76,7 @@ PROTOTYPES = {
     "qsv_expval_pauli_batch": (_i, [_vp, _u64, _vp, _vp, _vp, _vp]),
     "qsv_norm2": (_i, [_vp, _P(_dbl)]),
     "qsv_inner": (_i, [_vp, _vp, _P(_dbl)]),
+    "qsv_inner_static_scratch": (_i, [_i, _vp, _vp, _u64, _vp, _vp]),
     "qsv_probabilities": (_i, [_vp, _P(_i), _i, _vp]),
     "qsv_sample": (_i, [_vp, _P(_i), _i, _vp, _u64, _vp, _P(_dbl)]),
     "qsv_collapse": (_i, [_vp, _P(_i), _i, _u64, _dbl, _i]),

@@ -20,7 +20,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(CSRC, "_obj")
 LIB = os.path.join(HERE, "libqsv_b200.so")
 SOURCES = ["qsv_state.cu", "qsv_gate.cu", "qsv_expval.cu", "qsv_sample.cu", "qsv_dist.cu", "qsv_density.cu",
-           "qsv_counts.cu", "qsv_graph.cu"]
+           "qsv_counts.cu", "qsv_graph.cu", "qsv_noalloc.cu"]
 NVCC_FLAGS = [
     "-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
     "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function",
