@@ -342,6 +342,7 @@ def run_ours(args, dist: Dist) -> dict:
             result["roofline_unfused"] = roofline_gate_stream(args, device)
             result["gate_stream_30q"] = result["roofline_unfused"].pop("_detail")
             result["config0"] = config0_block(device, with_cpu=(dist.world == 1))
+            result["shared_prefix"] = shared_prefix_block(device, n, reps, obs)
             if dist.world == 1:
                 result["cpu_baseline"] = cpu_baseline(args)
             _lib.drain_pool()
@@ -351,6 +352,38 @@ def run_ours(args, dist: Dist) -> dict:
         if dist.rank == 0:
             result["sharded"] = sh
     return result
+
+
+def shared_prefix_block(device, n, reps, obs, sets: int = 16) -> dict:
+    """SURVEY.md 8f N1, shared-prefix caching (qiskit_b200/prefix_cache.py): the headline circuit and
+    observable with parameter sets that differ only in the LAST rotation layer (a sweep of the final
+    angles), through the public API with the cache on and off.  Not part of the headline metric: random
+    parameter sets share no prefix and never enter this path."""
+    from qiskit_b200 import StatevectorEstimator, _lib
+    from qiskit_b200 import circuit_library as lib
+
+    circuit = lib.efficient_su2_circuit(n, reps)
+    n_params = 2 * n * (reps + 1)
+    rng = np.random.default_rng(77)
+    theta = np.tile(rng.uniform(-np.pi, np.pi, n_params), (sets, 1))
+    theta[:, -2 * n:] = rng.uniform(-np.pi, np.pi, (sets, 2 * n))
+    out = {"workload": f"{n}q EfficientSU2 reps={reps}, {sets} parameter sets differing in the last rotation "
+                       f"layer only, {len(obs.coeffs)}-term observable, StatevectorEstimator.run"}
+    evs = {}
+    for label, on in (("cache_off", False), ("cache_on", True)):
+        est = StatevectorEstimator(device=device)
+        est._PREFIX_CACHE = on
+        est.run([(circuit, obs, theta)]).result()
+        t0 = time.perf_counter()
+        evs[label] = est.run([(circuit, obs, theta)]).result()[0].data.evs
+        out[label + "_ms_per_eval"] = 1e3 * (time.perf_counter() - t0) / sets
+        if on:
+            out["stats"] = est.last_prefix_stats
+        del est
+        _lib.drain_pool()
+    out["speedup"] = out["cache_off_ms_per_eval"] / out["cache_on_ms_per_eval"]
+    out["max_abs_diff_evs"] = float(np.max(np.abs(evs["cache_on"] - evs["cache_off"])))
+    return out
 
 
 def roofline_gate_stream(args, device) -> dict:

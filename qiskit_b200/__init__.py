@@ -10,6 +10,7 @@ from .exceptions import QiskitError
 from .circuit import (ClassicalRegister, Gate, Instruction, Parameter, ParameterVector,
                       QuantumCircuit)
 from .pauli import Pauli, PauliList, SparsePauliOp
+from .sparse_observable import SparseObservable
 from .statevector import Statevector
 from .densitymatrix import DensityMatrix
 from .primitives import BitArray, StatevectorEstimator, StatevectorSampler
@@ -19,7 +20,7 @@ from .backend_primitives import BackendEstimatorV2, BackendSamplerV2
 
 __all__ = [
     "QiskitError", "QuantumCircuit", "ClassicalRegister", "Parameter", "ParameterVector", "Gate",
-    "Instruction", "Pauli", "PauliList", "SparsePauliOp", "Statevector", "DensityMatrix", "StatevectorEstimator",
+    "Instruction", "Pauli", "PauliList", "SparsePauliOp", "SparseObservable", "Statevector", "DensityMatrix", "StatevectorEstimator",
     "StatevectorSampler", "BitArray", "BasicSimulator", "BackendEstimatorV2", "BackendSamplerV2", "sampled_expectation_value", "install",
 ]
 __version__ = "0.1.0"
