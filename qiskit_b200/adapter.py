@@ -26,6 +26,7 @@ CI and on the GPU box alike.  ``install()`` rebinds Qiskit's entry points to the
 from __future__ import annotations
 
 import copy as _copy
+import os
 from types import SimpleNamespace
 
 import numpy as np
@@ -62,6 +63,9 @@ def qiskit_namespace():
         PubResult=PubResult, SamplerPubResult=SamplerPubResult, PrimitiveResult=PrimitiveResult,
         PrimitiveJob=PrimitiveJob, bound_circuit_to_instruction=bound_circuit_to_instruction,
         preprocess_circuit=_preprocess_circuit)
+
+
+_PREFIX_CACHE = os.environ.get("QSV_PREFIX_CACHE", "1") != "0"
 
 
 def _has_stochastic_op(circuit) -> bool:
@@ -327,9 +331,19 @@ def make_adapter(ns, *, device: int = 0):
             # the reference re-simulates every broadcast index; without reset / initialize the state only
             # depends on the bound circuit, so consecutive indices that share it share the state
             reuse = not _has_stochastic_op(circuit)
+            self.last_prefix_stats = None
+            raw = self._shared_prefix_evs(pub, bound_circuits, bc_circuits, bc_obs) if reuse else None
             state, state_of = None, None
             for index in np.ndindex(*bc_circuits.shape):
                 bound_circuit = bc_circuits[index]
+                if raw is not None:
+                    expectation_value = raw[index]
+                    if precision != 0:
+                        if not np.isreal(expectation_value):
+                            raise ValueError("Given operator is not Hermitian and noise cannot be added.")
+                        expectation_value = rng.normal(expectation_value, precision)
+                    evs[index] = expectation_value
+                    continue
                 if not (reuse and state is not None and state_of is bound_circuit):
                     state = None     # hand the previous buffer back to the pool first
                     state = DeviceStatevector.from_int(0, 2 ** bound_circuit.num_qubits)
@@ -347,6 +361,47 @@ def make_adapter(ns, *, device: int = 0):
             data = ns.DataBin(evs=evs, stds=stds, shape=evs.shape)
             return ns.PubResult(data, metadata={"target_precision": precision,
                                                 "circuit_metadata": pub.circuit.metadata})
+
+        def _shared_prefix_evs(self, pub, bound_circuits, bc_circuits, bc_obs):
+            """Shared-prefix caching across the parameter sets of the pub (prefix_cache.py):
+            {broadcast index: expectation value}, or None when the sets share nothing (or the bindings
+            container cannot give its values as one array) and the serial loop below should run."""
+            from . import prefix_cache as pc
+
+            if not _PREFIX_CACHE or bound_circuits.size < 2:
+                return None
+            circuit = pub.circuit
+            try:
+                values = np.asarray(pub.parameter_values.as_array(list(circuit.parameters)), dtype=float)
+                values = values.reshape(bound_circuits.size, -1)
+                first_inst, total = pc.first_use(circuit)
+            except (AttributeError, TypeError, ValueError):
+                return None
+            order, share = pc.order_sets(values, first_inst, total)
+            if share.size == 0 or float(share.max()) < pc.MIN_SHARE:
+                return None
+            flat = list(bound_circuits.reshape(-1))
+            by_circuit = {}
+            for index in np.ndindex(*bc_circuits.shape):
+                by_circuit.setdefault(id(bc_circuits[index]), []).append(index)
+            n = circuit.num_qubits
+            raw = {}
+
+            def lower(sid):
+                stream = GateStream()
+                walk(None, ns.bound_circuit_to_instruction(flat[sid]), None, stream)
+                return stream
+
+            def consume(sid, dev):
+                state = DeviceStatevector(dev)               # adopts the engine state, no copy
+                for index in by_circuit.get(id(flat[sid]), ()):
+                    paulis, coeffs = zip(*bc_obs[index].items())
+                    raw[index] = np.real_if_close(state.expectation_value(ns.SparsePauliOp(paulis, coeffs)))
+
+            stats = pc.run_sets(order, lower, lambda: _DevSV.from_int(0, 1 << n, device=default_device), consume,
+                                lanes=1, can_checkpoint=lambda: pc._device_can_hold_checkpoint(n, default_device))
+            self.last_prefix_stats = stats.as_dict()
+            return raw
 
     class DeviceSampler(ns.BaseSamplerV2):
         """statevector_sampler.py:136-205 on the device engine."""

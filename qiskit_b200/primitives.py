@@ -711,6 +711,33 @@ class StatevectorSampler:
     def _run(self, pubs):
         return PrimitiveResult([self._run_pub(pub) for pub in pubs], metadata={"version": 2})
 
+    _PREFIX_CACHE = StatevectorEstimator._PREFIX_CACHE
+
+    def _run_shared_prefix(self, circuit, values_nd, indices, sample_into) -> bool:
+        """Shared-prefix caching (prefix_cache.py) for the parameter sets of a Sampler pub: the seeded
+        generator is per index (not shared across indices), so the visiting order does not change results."""
+        from . import prefix_cache as pc
+
+        if not self._PREFIX_CACHE or len(indices) < 2 or _has_reset(circuit) or circuit.num_qubits == 0:
+            return False
+        values = np.stack([np.asarray(values_nd[index], dtype=float) for index in indices])
+        first_inst, total = pc.first_use(circuit)
+        order, share = pc.order_sets(values, first_inst, total)
+        if share.size == 0 or float(share.max()) < pc.MIN_SHARE:
+            return False
+        n = circuit.num_qubits
+
+        def lower(sid):
+            stream = GateStream()
+            walk(None, _bound_instruction(circuit, values[sid]), None, stream)
+            return stream
+
+        stats = pc.run_sets(order, lower, lambda: Statevector.from_int(0, 1 << n, device=self._device),
+                            lambda sid, state: sample_into(indices[sid], state), lanes=1,
+                            can_checkpoint=lambda: pc._device_can_hold_checkpoint(n, self._device))
+        self.last_prefix_stats = stats.as_dict()
+        return True
+
     def _run_pub(self, pub: SamplerPub) -> SamplerPubResult:
         circuit, qargs, meas_info = _preprocess_circuit(pub.circuit)
         shape = pub.shape
@@ -718,10 +745,8 @@ class StatevectorSampler:
             item.creg_name: np.zeros(shape + (pub.shots, item.num_bytes), dtype=np.uint8)
             for item in meas_info
         }
-        for index in np.ndindex(*shape):
-            state = Statevector(_bound_instruction(circuit, pub.parameter_values[index]),
-                                device=self._device)
-            state.seed(self._seed)
+        def sample_into(index, state):
+            state.seed(self._seed)       # every index draws from its own generator (statevector_sampler.py:209)
             if qargs:
                 samples = state.sample_indices(pub.shots, qargs)
             else:
@@ -729,7 +754,15 @@ class StatevectorSampler:
             for item in meas_info:
                 arrays[item.creg_name][index] = pack_samples(samples, len(qargs), item.num_bits,
                                                              item.qreg_indices)
-            state = None
+
+        indices = list(np.ndindex(*shape))
+        self.last_prefix_stats = None
+        if not self._run_shared_prefix(circuit, pub.parameter_values, indices, sample_into):
+            for index in indices:
+                state = Statevector(_bound_instruction(circuit, pub.parameter_values[index]),
+                                    device=self._device)
+                sample_into(index, state)
+                state = None
         meas = {item.creg_name: BitArray(arrays[item.creg_name], item.num_bits) for item in meas_info}
         return SamplerPubResult(
             DataBin(**meas, shape=shape),

@@ -298,6 +298,9 @@ class BindingsArray:
 
     shape = property(lambda self: self._values.shape[:-1])
 
+    def as_array(self, parameters=None):
+        return self._values
+
     def bind_all(self, circuit):
         out = np.empty(self.shape, dtype=object)
         for idx in np.ndindex(*self.shape):

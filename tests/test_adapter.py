@@ -106,6 +106,45 @@ def test_device_primitives_reuse_the_reference_pub_containers():
     assert set(cb) == {0, 1} and abs(cb[0] - 1000) < 150
 
 
+@pytest.mark.gpu
+def test_device_estimator_shares_prefixes_across_parameter_sets():
+    """prefix_cache.py through the adapter: sets that differ only in the LAST parameter reuse the state
+    after the shared gates; values equal the serial loop's (cache off) and the oracle's."""
+    ad = adapter.make_adapter(fq.namespace())
+    th = ParameterVector("t", 3)
+    qc = fq.QuantumCircuit(3)
+    qc.ry(th[0], 0); qc.ry(th[1], 1)
+    for _ in range(4):
+        qc.h(2); qc.cx(0, 1); qc.cx(1, 2); qc.h(0)
+    qc.rz(th[2], 2); qc.h(2)
+    theta = np.array([[0.4, -1.1, x] for x in (2.2, -0.3, 0.9, 1.7)])
+
+    def oracle(v):
+        gates = [(ogm.ry(v[0]), [0]), (ogm.ry(v[1]), [1])]
+        for _ in range(4):
+            gates += [(ogm.h(), [2]), (ogm.cx(), [0, 1]), (ogm.cx(), [1, 2]), (ogm.h(), [0])]
+        gates += [(ogm.rz(v[2]), [2]), (ogm.h(), [2])]
+        return ref.apply_gate_list(ref.basis_state(3), gates)
+
+    est = ad.DeviceEstimator()
+    evs = est.run([(qc, ["ZIX", "IZZ"], theta[:, None, :])]).result()[0].data.evs
+    st = est.last_prefix_stats
+    assert st is not None and st["sets"] == 4 and st["checkpoints"] == 1
+    assert st["gates_applied"] == 20 + 3 * 2                     # one full stream, then two gates per set
+    adapter._PREFIX_CACHE = False
+    try:
+        est2 = ad.DeviceEstimator()
+        evs_off = est2.run([(qc, ["ZIX", "IZZ"], theta[:, None, :])]).result()[0].data.evs
+        assert est2.last_prefix_stats is None
+    finally:
+        adapter._PREFIX_CACHE = True
+    np.testing.assert_allclose(evs, evs_off, atol=1e-12)
+    for i in range(4):
+        psi = oracle(theta[i])
+        for j, label in enumerate(["ZIX", "IZZ"]):
+            assert abs(evs[i, j] - np.real(ref.expectation_value_labels(psi, [(label, 1.0)]))) < 1e-10
+
+
 def test_real_qiskit_if_importable():
     try:
         ad = adapter.device_classes()

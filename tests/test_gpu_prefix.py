@@ -102,3 +102,31 @@ def test_random_sets_keep_the_two_lane_path_and_reset_circuits_are_never_cached(
     assert est.last_prefix_stats is None
     r2 = StatevectorEstimator(seed=3).run([(rc, ["ZI", "IZ"], [[0.1], [0.1]])]).result()[0].data.evs
     np.testing.assert_array_equal(r1, r2)
+
+
+def test_sampler_parameter_sweep_is_identical_with_and_without_the_cache():
+    """StatevectorSampler seeds every index from the same seed (statevector_sampler.py:209), so the order
+    in which the cache visits the parameter sets cannot change any shot."""
+    from qiskit_b200 import StatevectorSampler
+
+    n, reps = 7, 2
+    qc = lib.efficient_su2_circuit(n, reps)
+    qc.measure_all()
+    p = len(qc.parameters)
+    rng = np.random.default_rng(2)
+    values = np.tile(rng.uniform(-np.pi, np.pi, p), (5, 1))
+    values[:, -2 * n:] = rng.uniform(-np.pi, np.pi, (5, 2 * n))       # last RY + RZ layer (RZ alone would not move any probability)
+    values = values[[2, 0, 4, 3, 1]]
+    out = {}
+    for cache in (True, False):
+        smp = StatevectorSampler(seed=11)
+        smp._PREFIX_CACHE = cache
+        res = smp.run([(qc, values)], shots=2000).result()[0]
+        out[cache] = res.data.meas.array.copy()
+        stats = smp.last_prefix_stats
+        assert (stats is not None) == cache
+        if cache:
+            assert stats["sets"] == 5 and stats["gates_applied"] < 0.6 * stats["gates_total"]
+    assert out[True].shape == (5, 2000, 1)
+    np.testing.assert_array_equal(out[True], out[False])
+    assert len({out[True][i].tobytes() for i in range(5)}) == 5          # the five sets really differ
