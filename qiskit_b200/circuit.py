@@ -75,6 +75,13 @@ class Instruction:
     def is_parameterized(self):
         return any(isinstance(p, Parameter) for p in self.params)
 
+    def __copy__(self):
+        # assign_parameters copies every operation of the circuit once per parameter set (host time on the
+        # Estimator's critical path): plain attribute copy instead of copy.copy's __reduce_ex__ round trip
+        new = object.__new__(type(self))
+        new.__dict__.update(self.__dict__)
+        return new
+
     def to_matrix(self):
         raise QiskitError(f"to_matrix not defined for {self.name}")
 
@@ -326,7 +333,7 @@ class QuantumCircuit:
 
     def copy_shallow(self):
         new = copy.copy(self)
-        new.data = [CircuitInstruction(copy.copy(i.operation), i.qubits, i.clbits) for i in self.data]
+        new.data = [CircuitInstruction(i.operation.__copy__(), i.qubits, i.clbits) for i in self.data]
         for inst in new.data:
             inst.operation.params = list(inst.operation.params)
         new.cregs = list(self.cregs)

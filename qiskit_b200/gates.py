@@ -14,15 +14,24 @@ _SQ = np.sqrt(0.5)
 
 
 class GateDef:
-    __slots__ = ("name", "num_qubits", "num_params", "fn", "diagonal")
+    __slots__ = ("name", "num_qubits", "num_params", "fn", "diagonal", "_const")
 
     def __init__(self, name, num_qubits, num_params, fn, diagonal=False):
         self.name, self.num_qubits, self.num_params = name, num_qubits, num_params
         self.fn, self.diagonal = fn, diagonal
+        self._const = None
 
     def matrix(self, params=()):
         if len(params) != self.num_params:
             raise ValueError(f"gate {self.name} takes {self.num_params} parameters, got {len(params)}")
+        if self.num_params == 0:
+            # parameter-free gates (the CX chain of an ansatz is a third of its gates): built once, shared
+            # read-only -- lowering a bound circuit is host time on the Estimator's critical path
+            if self._const is None:
+                m = np.ascontiguousarray(self.fn(), dtype=np.complex128)
+                m.flags.writeable = False
+                self._const = m
+            return self._const
         return np.asarray(self.fn(*[float(p) for p in params]), dtype=np.complex128)
 
 
